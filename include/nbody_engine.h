@@ -1,0 +1,136 @@
+/*
+ * nbody_engine.h -- C ABI of the B200-native gravitational N-body engine.
+ *
+ * This is the drop-in boundary for the reference's exhaustive (direct-sum)
+ * path and its Barnes-Hut variant.  The reference (Metgraph/N-Body-simulation)
+ * has no plugin/FFI layer of its own: inside each program the boundary is the
+ * pair of C functions propagation()/acceleration().  Each entry point below
+ * names the reference code it stands in for.  Plain pointers and sizes only;
+ * no torch / C++ types.  The library is libnbody_b200.so (CUDA, sm_100a);
+ * there is no CPU fallback: without a usable CUDA device nb_init fails with
+ * NB_E_NODEVICE.
+ *
+ * Array packing is the reference CUDA host's (cuda/exhaustive.cu:240-251):
+ *     pos_xyzm[4*i + 0..3] = x, y, z, mass          vel_xyz[3*i + 0..2] = vx, vy, vz
+ * All host arrays are double (the reference is FP64 everywhere); an FP32
+ * engine rounds them to float at nb_init / nb_upload.
+ *
+ * Threading: one host thread per engine.  nb_step only enqueues work on the
+ * engine's stream; nb_gather / nb_sync wait for it.
+ */
+#ifndef NBODY_ENGINE_H
+#define NBODY_ENGINE_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct nb_engine nb_engine;
+
+/* return codes: 0 on success, negative otherwise (never exit() inside the
+ * library; the host maps failures to the reference's exit(EXIT_FAILURE),
+ * cuda/exhaustive.cu:78-84) */
+#define NB_OK 0
+#define NB_E_INVALID (-1)  /* bad argument / configuration */
+#define NB_E_CUDA (-2)     /* CUDA runtime error (see nb_last_error) */
+#define NB_E_NOMEM (-3)    /* host or device allocation failed */
+#define NB_E_COMM (-4)     /* NCCL missing or failed */
+#define NB_E_NODEVICE (-5) /* no CUDA device: there is no CPU fallback */
+#define NB_E_STATE (-6)    /* call not valid in the engine's current state */
+
+#define NB_PREC_FP64 0 /* the reference's precision */
+#define NB_PREC_FP32 1 /* production / roofline precision */
+
+#define NB_ALGO_DIRECT 0     /* O(N^2) exhaustive sum: cuda/exhaustive.cu, serial/exhaustive.c */
+#define NB_ALGO_BARNES_HUT 1 /* THETA-criterion octree: cuda/barnes-hut.cu, serial/barnes-hut.c */
+
+#define NB_COMM_ID_BYTES 128 /* sizeof(ncclUniqueId) */
+
+typedef struct nb_config {
+    int precision; /* NB_PREC_* */
+    int algorithm; /* NB_ALGO_* */
+    double dt;     /* time step; the host passes (double)strtof(argv[4]) as the reference does
+                      (serial/exhaustive.c:43,51; cuda/exhaustive.cu:49,56) */
+    double eps2;   /* softening, reference literal 0.01 (serial/exhaustive.c:172) */
+    double G;      /* BIG_G = 1.0 (serial/exhaustive.c:24) */
+    double theta;  /* THETA = 0.5 (serial/barnes-hut.c:40); Barnes-Hut only */
+    int device;    /* CUDA device ordinal this engine (rank) runs on */
+    int rank;      /* i-slice owner index, 0 <= rank < world */
+    int world;     /* number of ranks sharing the bodies (1 = single GPU) */
+    const void *comm_id; /* world > 1: NB_COMM_ID_BYTES from nb_comm_id() of rank 0 */
+    int tune_ctas_per_sm; /* 0 = engine default; launch geometry is ours (the reference's
+                             grid_size/block_size argv are accepted and ignored) */
+    int tune_flags;       /* 0 = default; NB_TUNE_* bits, for experiments only */
+} nb_config;
+
+#define NB_TUNE_SCALAR_FP32 1 /* FP32 kernel without packed f32x2 instructions */
+#define NB_TUNE_NO_SPLIT 2    /* one CTA per i-block over all j (no j-range splitting) */
+
+typedef struct nb_stats {
+    double last_step_ms;        /* device time (CUDA events on the engine stream) of the last nb_step */
+    double last_force_ms;       /* device time of the last force kernel alone */
+    unsigned long long force_launches; /* force-kernel launches since nb_init */
+    unsigned long long kernel_launches; /* all engine kernel launches since nb_init */
+    unsigned long long interactions;   /* pairwise interactions evaluated by this rank since nb_init */
+    unsigned long long steps_done;     /* completed drifts */
+    int grid, block, smem_bytes;       /* geometry of the last force launch */
+    size_t n, n_padded, slice_begin, slice_end;
+} nb_stats;
+
+/* Fills cfg with the reference's constants: FP64, direct, eps2 = 0.01, G = 1,
+ * theta = 0.5, dt = (double)0.01f, device 0, world 1. */
+void nb_config_default(nb_config *cfg);
+
+/* Replaces the allocation + H2D prologue of propagation()
+ * (cuda/exhaustive.cu:116-129).  Copies the n bodies in; the caller keeps
+ * ownership of the host arrays.  Every rank passes ALL n bodies. */
+int nb_init(nb_engine **e, const nb_config *cfg, size_t n, const double *pos_xyzm,
+            const double *vel_xyz);
+
+/* Re-loads positions/velocities of an existing engine (same n), resetting the
+ * step counter: the H2D half of the end-to-end benchmark. */
+int nb_upload(nb_engine *e, const double *pos_xyzm, const double *vel_xyz);
+
+/* Advances n_steps of kick-drift-kick leapfrog: the time loop of propagation()
+ * (serial/exhaustive.c:218-250, cuda/exhaustive.cu:135-151).  One fused
+ * force+integrate launch per step; a run of n steps followed by nb_gather
+ * with velocities costs n+1 force evaluations, like the reference. */
+int nb_step(nb_engine *e, int n_steps);
+
+/* Copies the current state out: what the reference reads back at
+ * cuda/exhaustive.cu:153-165 (positions+mass of the current frame) plus the
+ * synchronised velocities v_k.  vel_xyz may be NULL (frame output needs
+ * positions only).  Blocks until the engine's stream is idle. */
+int nb_gather(nb_engine *e, double *pos_xyzm, double *vel_xyz);
+
+/* acceleration() on the current positions (serial/exhaustive.c:155-181,
+ * cuda/exhaustive.cu:273-338, or the Barnes-Hut evaluation): acc_xyz[3n].
+ * Does not advance the state. */
+int nb_accelerations(nb_engine *e, double *acc_xyz);
+
+/* get_energy() of common/get_energy.c:7-47 on the current state, on the GPU
+ * (KE, unsoftened PE over i <= j). */
+int nb_energy(nb_engine *e, double *KE, double *PE);
+
+int nb_sync(nb_engine *e);
+int nb_get_stats(nb_engine *e, nb_stats *out);
+
+/* Releases every device allocation, stream and communicator
+ * (cuda/exhaustive.cu:167-169). */
+void nb_free(nb_engine *e);
+
+/* Multi-rank plumbing: rank 0 creates an id, the host distributes it. */
+int nb_comm_id(void *id_out, size_t bytes);
+
+const char *nb_strerror(int code);
+/* Detail of the last failure on this thread (CUDA / NCCL message). */
+const char *nb_last_error(void);
+int nb_device_count(void);
+const char *nb_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NBODY_ENGINE_H */

@@ -1,0 +1,228 @@
+// nb_aux.cu -- O(N) helper kernels around the force kernels:
+//   pack / unpack between the host packing of the reference
+//   (pos_xyzm[4i..], vel_xyz[3i..]; cuda/exhaustive.cu:240-251) and the device
+//   layouts (nb_direct.cuh), the stand-alone kick+drift used when a(x_k) is
+//   already stored (serial/exhaustive.c:221-232), and get_energy
+//   (common/get_energy.c:7-47) as an O(N^2) FP64 kernel.
+#include "nb_aux.cuh"
+
+namespace nb {
+namespace {
+
+__global__ void pack_f32_kernel(const double *__restrict__ pos, const double *__restrict__ vel,
+                                unsigned n, unsigned n_quads, float4 *__restrict__ q0,
+                                float4 *__restrict__ q1, float4 *__restrict__ v)
+{
+    const unsigned iq = blockIdx.x * blockDim.x + threadIdx.x;
+    if (iq >= n_quads) return;
+    float c[7][4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const unsigned b = iq * 4 + r;
+        const bool real = b < n;
+        c[0][r] = real ? (float)pos[4 * (size_t)b + 0] : 0.f;
+        c[1][r] = real ? (float)pos[4 * (size_t)b + 1] : 0.f;
+        c[2][r] = real ? (float)pos[4 * (size_t)b + 2] : 0.f;
+        c[3][r] = real ? (float)pos[4 * (size_t)b + 3] : 0.f;
+        c[4][r] = (real && vel) ? (float)vel[3 * (size_t)b + 0] : 0.f;
+        c[5][r] = (real && vel) ? (float)vel[3 * (size_t)b + 1] : 0.f;
+        c[6][r] = (real && vel) ? (float)vel[3 * (size_t)b + 2] : 0.f;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float4 f = make_float4(c[k][0], c[k][1], c[k][2], c[k][3]);
+        q0[(size_t)iq * 4 + k] = f;
+        q1[(size_t)iq * 4 + k] = f;
+    }
+    if (v) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+            v[(size_t)iq * 3 + k] = make_float4(c[4 + k][0], c[4 + k][1], c[4 + k][2], c[4 + k][3]);
+    }
+}
+
+__global__ void pack_f64_kernel(const double *__restrict__ pos, const double *__restrict__ vel,
+                                unsigned n, unsigned n_pad, double4 *__restrict__ q0,
+                                double4 *__restrict__ q1, double4 *__restrict__ v)
+{
+    const unsigned b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n_pad) return;
+    const bool real = b < n;
+    const double4 p = real ? make_double4(pos[4 * (size_t)b], pos[4 * (size_t)b + 1],
+                                          pos[4 * (size_t)b + 2], pos[4 * (size_t)b + 3])
+                           : make_double4(0, 0, 0, 0);
+    q0[b] = p;
+    q1[b] = p;
+    if (v)
+        v[b] = (real && vel) ? make_double4(vel[3 * (size_t)b], vel[3 * (size_t)b + 1],
+                                            vel[3 * (size_t)b + 2], 0.0)
+                             : make_double4(0, 0, 0, 0);
+}
+
+// planes = 4: positions+mass -> out[4b..]; planes = 3: vel / acc -> out[3b..]
+__global__ void unpack_f32_kernel(const float4 *__restrict__ src, unsigned n, int planes,
+                                  double *__restrict__ out)
+{
+    const unsigned b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n) return;
+    const float *f = reinterpret_cast<const float *>(src) + (size_t)(b >> 2) * (planes * 4) + (b & 3);
+    for (int k = 0; k < planes; ++k) out[(size_t)planes * b + k] = (double)f[k * 4];
+}
+
+__global__ void unpack_f64_kernel(const double4 *__restrict__ src, unsigned n, int planes,
+                                  double *__restrict__ out)
+{
+    const unsigned b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n) return;
+    const double4 p = src[b];
+    out[(size_t)planes * b + 0] = p.x;
+    out[(size_t)planes * b + 1] = p.y;
+    out[(size_t)planes * b + 2] = p.z;
+    if (planes == 4) out[(size_t)planes * b + 3] = p.w;
+}
+
+__global__ void kickdrift_f32_kernel(const float4 *__restrict__ qc, float4 *__restrict__ qn,
+                                     float4 *__restrict__ vel, const float4 *__restrict__ acc,
+                                     unsigned i_begin, unsigned i_end, unsigned n_real, float dt)
+{
+    const unsigned iq = i_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (iq >= i_end) return;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const float4 X = qc[(size_t)iq * 4 + c], V = vel[(size_t)iq * 3 + c],
+                     A = acc[(size_t)iq * 3 + c];
+        float x[4] = {X.x, X.y, X.z, X.w}, v[4] = {V.x, V.y, V.z, V.w};
+        const float a[4] = {A.x, A.y, A.z, A.w};
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            if (iq * 4u + r >= n_real) continue;
+            v[r] = __fadd_rn(v[r], __fmul_rn(__fmul_rn(a[r], dt), 0.5f));
+            x[r] = __fadd_rn(x[r], __fmul_rn(v[r], dt));
+        }
+        vel[(size_t)iq * 3 + c] = make_float4(v[0], v[1], v[2], v[3]);
+        qn[(size_t)iq * 4 + c] = make_float4(x[0], x[1], x[2], x[3]);
+    }
+}
+
+__global__ void kickdrift_f64_kernel(const double4 *__restrict__ qc, double4 *__restrict__ qn,
+                                     double4 *__restrict__ vel, const double4 *__restrict__ acc,
+                                     unsigned i_begin, unsigned i_end, unsigned n_real, double dt)
+{
+    const unsigned b = i_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= i_end || b >= n_real) return;
+    double4 X = qc[b], V = vel[b];
+    const double4 A = acc[b];
+    V.x = __dadd_rn(V.x, __dmul_rn(__dmul_rn(A.x, dt), 0.5));
+    V.y = __dadd_rn(V.y, __dmul_rn(__dmul_rn(A.y, dt), 0.5));
+    V.z = __dadd_rn(V.z, __dmul_rn(__dmul_rn(A.z, dt), 0.5));
+    X.x = __dadd_rn(X.x, __dmul_rn(V.x, dt));
+    X.y = __dadd_rn(X.y, __dmul_rn(V.y, dt));
+    X.z = __dadd_rn(X.z, __dmul_rn(V.z, dt));
+    vel[b] = V;
+    qn[b] = X;
+}
+
+// get_energy: KE = 1/2 sum m v^2 ; PE = -G sum_{i<j} m_i m_j / r_ij (r = 0 pairs
+// contribute 0, common/get_energy.c:38-40).  One thread per i, j > i tiles in
+// shared memory, block partials written out and added on the host in order.
+constexpr int ETB = 256;
+__global__ void energy_kernel(const double *__restrict__ pos, const double *__restrict__ vel,
+                              unsigned n, double *__restrict__ partial /* [grid][2] */)
+{
+    __shared__ double4 tile[ETB];
+    __shared__ double red[2][ETB / 32];
+    const unsigned i = blockIdx.x * ETB + threadIdx.x;
+    const bool real = i < n;
+    double xi = 0, yi = 0, zi = 0, mi = 0, ke = 0, pe = 0;
+    if (real) {
+        xi = pos[4 * (size_t)i]; yi = pos[4 * (size_t)i + 1]; zi = pos[4 * (size_t)i + 2];
+        mi = pos[4 * (size_t)i + 3];
+        const double vx = vel[3 * (size_t)i], vy = vel[3 * (size_t)i + 1], vz = vel[3 * (size_t)i + 2];
+        ke = mi * (vx * vx + vy * vy + vz * vz);
+    }
+    for (unsigned j0 = blockIdx.x * ETB; j0 < n; j0 += ETB) {
+        const unsigned j = j0 + threadIdx.x;
+        tile[threadIdx.x] = j < n ? make_double4(pos[4 * (size_t)j], pos[4 * (size_t)j + 1],
+                                                 pos[4 * (size_t)j + 2], pos[4 * (size_t)j + 3])
+                                  : make_double4(0, 0, 0, 0);
+        __syncthreads();
+        const unsigned lim = min((unsigned)ETB, n - j0);
+        for (unsigned k = 0; k < lim; ++k) {
+            if (j0 + k <= i) continue;
+            const double4 b = tile[k];
+            const double dx = b.x - xi, dy = b.y - yi, dz = b.z - zi;
+            const double r = sqrt(dx * dx + dy * dy + dz * dz);
+            pe += r > 0 ? (mi * b.w) / r : 0.0;
+        }
+        __syncthreads();
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        ke += __shfl_xor_sync(0xffffffffu, ke, o);
+        pe += __shfl_xor_sync(0xffffffffu, pe, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        red[0][threadIdx.x >> 5] = ke;
+        red[1][threadIdx.x >> 5] = pe;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0, b = 0;
+        for (int w = 0; w < ETB / 32; ++w) { a += red[0][w]; b += red[1][w]; }
+        partial[2 * blockIdx.x] = a;
+        partial[2 * blockIdx.x + 1] = b;
+    }
+}
+
+inline unsigned cdiv(unsigned a, unsigned b) { return (a + b - 1) / b; }
+} // namespace
+
+cudaError_t pack_bodies(int precision, const double *pos, const double *vel, unsigned n,
+                        unsigned n_units, void *q0, void *q1, void *v, cudaStream_t s)
+{
+    if (precision == 1)
+        pack_f32_kernel<<<cdiv(n_units, 256), 256, 0, s>>>(pos, vel, n, n_units, (float4 *)q0,
+                                                          (float4 *)q1, (float4 *)v);
+    else
+        pack_f64_kernel<<<cdiv(n_units, 256), 256, 0, s>>>(pos, vel, n, n_units, (double4 *)q0,
+                                                          (double4 *)q1, (double4 *)v);
+    return cudaGetLastError();
+}
+
+cudaError_t unpack_bodies(int precision, const void *src, unsigned n, int planes, double *out,
+                          cudaStream_t s)
+{
+    if (n == 0) return cudaSuccess;
+    if (precision == 1)
+        unpack_f32_kernel<<<cdiv(n, 256), 256, 0, s>>>((const float4 *)src, n, planes, out);
+    else
+        unpack_f64_kernel<<<cdiv(n, 256), 256, 0, s>>>((const double4 *)src, n, planes, out);
+    return cudaGetLastError();
+}
+
+cudaError_t kickdrift(int precision, const void *qc, void *qn, void *vel, const void *acc,
+                      unsigned i_begin, unsigned i_end, unsigned n_real, double dt, cudaStream_t s)
+{
+    if (i_end <= i_begin) return cudaSuccess;
+    const unsigned cnt = i_end - i_begin;
+    if (precision == 1)
+        kickdrift_f32_kernel<<<cdiv(cnt, 256), 256, 0, s>>>((const float4 *)qc, (float4 *)qn,
+                                                           (float4 *)vel, (const float4 *)acc,
+                                                           i_begin, i_end, n_real, (float)dt);
+    else
+        kickdrift_f64_kernel<<<cdiv(cnt, 256), 256, 0, s>>>((const double4 *)qc, (double4 *)qn,
+                                                           (double4 *)vel, (const double4 *)acc,
+                                                           i_begin, i_end, n_real, dt);
+    return cudaGetLastError();
+}
+
+unsigned energy_blocks(unsigned n) { return cdiv(n, ETB); }
+
+cudaError_t energy_partials(const double *pos_xyzm, const double *vel_xyz, unsigned n,
+                            double *partial, cudaStream_t s)
+{
+    if (n == 0) return cudaSuccess;
+    energy_kernel<<<energy_blocks(n), ETB, 0, s>>>(pos_xyzm, vel_xyz, n, partial);
+    return cudaGetLastError();
+}
+
+} // namespace nb

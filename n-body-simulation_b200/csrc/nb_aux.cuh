@@ -1,0 +1,22 @@
+// nb_aux.cuh -- launchers of the O(N) helper kernels (nb_aux.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+namespace nb {
+
+// host packing (device copies of pos_xyzm[4n], vel_xyz[3n] or nullptr) -> device layout;
+// both position buffers are filled (masses and padding never change afterwards).
+cudaError_t pack_bodies(int precision, const double *pos, const double *vel, unsigned n,
+                        unsigned n_units, void *q0, void *q1, void *v, cudaStream_t s);
+// device layout -> host packing; planes = 4 (pos+mass) or 3 (vel / acc)
+cudaError_t unpack_bodies(int precision, const void *src, unsigned n, int planes, double *out,
+                          cudaStream_t s);
+// v += (a*dt)/2 ; x' = x + v*dt from stored accelerations, units [i_begin, i_end)
+cudaError_t kickdrift(int precision, const void *qc, void *qn, void *vel, const void *acc,
+                      unsigned i_begin, unsigned i_end, unsigned n_real, double dt, cudaStream_t s);
+unsigned energy_blocks(unsigned n);
+// partial[2*b] = sum m v^2, partial[2*b+1] = sum_{i<j} m_i m_j / r_ij of block b
+cudaError_t energy_partials(const double *pos_xyzm, const double *vel_xyz, unsigned n,
+                            double *partial, cudaStream_t s);
+
+} // namespace nb

@@ -1,0 +1,420 @@
+// nb_direct_f32.cu -- the FP32 O(N^2) force + leapfrog kernel for sm_100a.
+//
+// Replaces acceleration<<<>>> + update_velocities<<<>>> + update_positions<<<>>>
+// of the reference (cuda/exhaustive.cu:273-388; math of serial/exhaustive.c:155-181
+// and :218-250) with ONE launch per step:
+//   * bodies live in HBM as 64-byte quads {X4,Y4,Z4,M4}; a thread owns one quad
+//     = a register block of 4 i-bodies (3 x 128-bit loads);
+//   * j-bodies stream through a 4-stage shared-memory ring filled by 1-D bulk
+//     async copies (TMA, SASS UBLKCP) from a dedicated producer warp and handed
+//     over with mbarriers; every compute warp reads a j-quad with four
+//     broadcast LDS.128;
+//   * the inner loop works on PAIRS of j-bodies with the sm_100 packed FP32
+//     instructions (FADD2/FFMA2/FMUL2): per 2 interactions 3 FADD2 + 6 FFMA2 +
+//     3 FMUL2 + 2 MUFU.RSQ, i.e. 12 FMA-pipe lane-operations and one MUFU per
+//     interaction in 7 issue slots;
+//   * FP32 partial sums are flushed into FP64 running sums once per tile
+//     (256 j-bodies), so the 1e6-term sums keep ~1e-7 relative accuracy;
+//   * the (i-block x j-tile) work list is cut evenly over a persistent grid
+//     (nb_common.cuh WorkSplit), the last CTA to finish an i-block adds the
+//     partial slots in fixed order and runs the kick/drift epilogue, so
+//     positions and velocities make one HBM round trip per step.
+#include "nb_direct.cuh"
+
+namespace nb {
+namespace {
+
+constexpr int STAGES = 4;
+
+__device__ __forceinline__ void named_sync(int id, int nthreads)
+{
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// One j-pair against the thread's four i-bodies, packed f32x2 arithmetic.
+// nxi/nyi/nzi hold -x_i etc. (ptxas folds the negation and the scalar
+// broadcast into the FADD2 operand: "FADD2 R, Rj.F32x2.HI_LO, -Ri.F32").
+__device__ __forceinline__ void pair_packed(float2 xj, float2 yj, float2 zj, float2 mj,
+                                            const float4 &XI, const float4 &YI, const float4 &ZI,
+                                            float2 e2, float2 (&ax)[4], float2 (&ay)[4],
+                                            float2 (&az)[4])
+{
+    const float xi[4] = {XI.x, XI.y, XI.z, XI.w};
+    const float yi[4] = {YI.x, YI.y, YI.z, YI.w};
+    const float zi[4] = {ZI.x, ZI.y, ZI.z, ZI.w};
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        float2 dx = __fadd2_rn(xj, make_float2(-xi[r], -xi[r]));
+        float2 dy = __fadd2_rn(yj, make_float2(-yi[r], -yi[r]));
+        float2 dz = __fadd2_rn(zj, make_float2(-zi[r], -zi[r]));
+        float2 r2 = __ffma2_rn(dx, dx, e2);
+        r2 = __ffma2_rn(dy, dy, r2);
+        r2 = __ffma2_rn(dz, dz, r2);
+        float2 ri = make_float2(rsqrt_approx(r2.x), rsqrt_approx(r2.y));
+        float2 ri2 = __fmul2_rn(ri, ri);
+        float2 mr = __fmul2_rn(mj, ri);
+        float2 s = __fmul2_rn(ri2, mr);
+        ax[r] = __ffma2_rn(dx, s, ax[r]);
+        ay[r] = __ffma2_rn(dy, s, ay[r]);
+        az[r] = __ffma2_rn(dz, s, az[r]);
+    }
+}
+
+// Scalar twin (NB_TUNE_SCALAR_FP32), for A/B measurements of the packed path.
+__device__ __forceinline__ void quad_scalar(const float4 &JX, const float4 &JY, const float4 &JZ,
+                                            const float4 &JM, const float4 &XI, const float4 &YI,
+                                            const float4 &ZI, float e2, float2 (&ax)[4],
+                                            float2 (&ay)[4], float2 (&az)[4])
+{
+    const float xi[4] = {XI.x, XI.y, XI.z, XI.w};
+    const float yi[4] = {YI.x, YI.y, YI.z, YI.w};
+    const float zi[4] = {ZI.x, ZI.y, ZI.z, ZI.w};
+    const float xj[4] = {JX.x, JX.y, JX.z, JX.w};
+    const float yj[4] = {JY.x, JY.y, JY.z, JY.w};
+    const float zj[4] = {JZ.x, JZ.y, JZ.z, JZ.w};
+    const float mj[4] = {JM.x, JM.y, JM.z, JM.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            float dx = xj[j] - xi[r], dy = yj[j] - yi[r], dz = zj[j] - zi[r];
+            float r2 = fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, e2)));
+            float ri = rsqrt_approx(r2);
+            float s = (ri * ri) * (mj[j] * ri);
+            ax[r].x = fmaf(dx, s, ax[r].x);
+            ay[r].x = fmaf(dy, s, ay[r].x);
+            az[r].x = fmaf(dz, s, az[r].x);
+        }
+    }
+}
+
+// kick / drift on one quad component, written with explicit roundings so the
+// operation order is the reference's: v += (a*dt)/2 ; x += v*dt
+// (serial/exhaustive.c:221-232).
+__device__ __forceinline__ float kick(float v, float a, float dt)
+{
+    return __fadd_rn(v, __fmul_rn(__fmul_rn(a, dt), 0.5f));
+}
+__device__ __forceinline__ float drift(float x, float v, float dt)
+{
+    return __fadd_rn(x, __fmul_rn(v, dt));
+}
+
+template <int NW, int TQ, bool PACKED, int MINB>
+__global__ void __launch_bounds__((NW + 1) * 32, MINB)
+    direct_f32_kernel(const StepParams p)
+{
+    constexpr int QPB = NW * 32; // quads (threads) per i-block
+    __shared__ __align__(128) float4 tiles[STAGES][TQ * 4];
+    __shared__ __align__(8) uint64_t full_bar[STAGES];
+    __shared__ __align__(8) uint64_t empty_bar[STAGES];
+    __shared__ unsigned s_last;
+    // FP64 running sums live in shared memory (12 per thread, touched once per
+    // tile) so the inner loop keeps its registers for the 4x2 interaction block.
+    __shared__ double dacc[12][QPB];
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const float4 *__restrict__ q = static_cast<const float4 *>(p.q_cur);
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], NW);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    const unsigned long long w0 = p.ws.bound(blockIdx.x);
+    const unsigned long long w1 = p.ws.bound(blockIdx.x + 1);
+    const unsigned n_jtiles = p.ws.n_jtiles;
+
+    if (warp == NW) {
+        // ---------------- producer warp: one lane feeds the ring ----------------
+        if (lane == 0) {
+            unsigned stage = 0, phase = 0;
+            unsigned t = (unsigned)(w0 % n_jtiles);
+            for (unsigned long long w = w0; w < w1; ++w) {
+                mbar_wait(&empty_bar[stage], phase ^ 1u);
+                const unsigned first = t * TQ;
+                const unsigned nq = min((unsigned)TQ, p.n_units - first);
+                const unsigned bytes = nq * 64u;
+                mbar_arrive_expect_tx(&full_bar[stage], bytes);
+                tma_load_1d(&tiles[stage][0], q + (size_t)first * 4, bytes, &full_bar[stage]);
+                if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+                if (++t == n_jtiles) t = 0;
+            }
+        }
+        return;
+    }
+
+    // -------------------------- compute warps -----------------------------------
+    const int tidc = threadIdx.x; // 0 .. QPB-1
+    const float dtf = (float)p.dt;
+    const float e2s = (float)p.eps2;
+    const float2 e2 = make_float2(e2s, e2s);
+    unsigned stage = 0, phase = 0;
+
+    unsigned long long w = w0;
+    while (w < w1) {
+        const unsigned ib = (unsigned)(w / n_jtiles);
+        const unsigned t0 = (unsigned)(w - (unsigned long long)ib * n_jtiles);
+        const unsigned cnt = (unsigned)min((unsigned long long)(n_jtiles - t0), w1 - w);
+        const unsigned iq = p.i_begin + ib * QPB + tidc;
+        const bool valid = iq < p.i_end;
+        const unsigned iqc = valid ? iq : p.i_begin;
+        const float4 XI = q[(size_t)iqc * 4 + 0];
+        const float4 YI = q[(size_t)iqc * 4 + 1];
+        const float4 ZI = q[(size_t)iqc * 4 + 2];
+
+#pragma unroll
+        for (int c = 0; c < 12; ++c) dacc[c][tidc] = 0.0;
+
+        for (unsigned k = 0; k < cnt; ++k) {
+            const unsigned first = (t0 + k) * TQ;
+            const int nq = (int)min((unsigned)TQ, p.n_units - first);
+            float2 ax[4], ay[4], az[4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) ax[r] = ay[r] = az[r] = make_float2(0.f, 0.f);
+
+            mbar_wait(&full_bar[stage], phase);
+            const float4 *__restrict__ tile = &tiles[stage][0];
+#pragma unroll 2
+            for (int jq = 0; jq < nq; ++jq) {
+                const float4 JX = tile[jq * 4 + 0];
+                const float4 JY = tile[jq * 4 + 1];
+                const float4 JZ = tile[jq * 4 + 2];
+                const float4 JM = tile[jq * 4 + 3];
+                if (PACKED) {
+                    pair_packed(make_float2(JX.x, JX.y), make_float2(JY.x, JY.y),
+                                make_float2(JZ.x, JZ.y), make_float2(JM.x, JM.y), XI, YI, ZI, e2,
+                                ax, ay, az);
+                    pair_packed(make_float2(JX.z, JX.w), make_float2(JY.z, JY.w),
+                                make_float2(JZ.z, JZ.w), make_float2(JM.z, JM.w), XI, YI, ZI, e2,
+                                ax, ay, az);
+                } else {
+                    quad_scalar(JX, JY, JZ, JM, XI, YI, ZI, e2s, ax, ay, az);
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty_bar[stage]);
+            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+            // flush the tile's FP32 partials into the FP64 running sums
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                dacc[0 + r][tidc] += (double)(ax[r].x + ax[r].y);
+                dacc[4 + r][tidc] += (double)(ay[r].x + ay[r].y);
+                dacc[8 + r][tidc] += (double)(az[r].x + az[r].y);
+            }
+        }
+        w += cnt;
+        double dax[4], day[4], daz[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            dax[r] = dacc[0 + r][tidc];
+            day[r] = dacc[4 + r][tidc];
+            daz[r] = dacc[8 + r][tidc];
+        }
+
+        // ---------------- combine partial j-ranges of this i-block ----------------
+        bool do_epilogue = true;
+        if (cnt != n_jtiles) {
+            const unsigned long long x0 = (unsigned long long)ib * n_jtiles;
+            const unsigned c_first = p.ws.owner(x0);
+            const unsigned c_last = p.ws.owner(x0 + n_jtiles - 1);
+            const unsigned nslots = c_last - c_first + 1;
+            const unsigned slot = blockIdx.x - c_first;
+            double2 *ws = reinterpret_cast<double2 *>(p.workspace) +
+                          ((size_t)ib * p.max_slots) * (size_t)(QPB * 6);
+            double2 *mine = ws + (size_t)slot * (QPB * 6);
+            mine[0 * QPB + tidc] = make_double2(dax[0], dax[1]);
+            mine[1 * QPB + tidc] = make_double2(dax[2], dax[3]);
+            mine[2 * QPB + tidc] = make_double2(day[0], day[1]);
+            mine[3 * QPB + tidc] = make_double2(day[2], day[3]);
+            mine[4 * QPB + tidc] = make_double2(daz[0], daz[1]);
+            mine[5 * QPB + tidc] = make_double2(daz[2], daz[3]);
+            __threadfence();
+            named_sync(1, QPB);
+            if (tidc == 0) {
+                const unsigned old = atomicAdd(&p.counters[ib], 1u);
+                const unsigned last = (old == nslots - 1);
+                if (last) p.counters[ib] = 0; // ready for the next launch
+                s_last = last;
+            }
+            named_sync(1, QPB);
+            do_epilogue = (s_last != 0);
+            if (do_epilogue) {
+                __threadfence();
+#pragma unroll
+                for (int r = 0; r < 4; ++r) dax[r] = day[r] = daz[r] = 0.0;
+                for (unsigned s = 0; s < nslots; ++s) {
+                    const double2 *src = ws + (size_t)s * (QPB * 6);
+                    double2 v;
+                    v = __ldcg(&src[0 * QPB + tidc]); dax[0] += v.x; dax[1] += v.y;
+                    v = __ldcg(&src[1 * QPB + tidc]); dax[2] += v.x; dax[3] += v.y;
+                    v = __ldcg(&src[2 * QPB + tidc]); day[0] += v.x; day[1] += v.y;
+                    v = __ldcg(&src[3 * QPB + tidc]); day[2] += v.x; day[3] += v.y;
+                    v = __ldcg(&src[4 * QPB + tidc]); daz[0] += v.x; daz[1] += v.y;
+                    v = __ldcg(&src[5 * QPB + tidc]); daz[2] += v.x; daz[3] += v.y;
+                }
+            }
+            named_sync(1, QPB); // s_last may be rewritten by the next i-block
+        }
+
+        // ---------------- epilogue: kick2 / kick1 / drift, one HBM round trip ------
+        if (do_epilogue && valid) {
+            float a[3][4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                a[0][r] = (float)(p.G * dax[r]);
+                a[1][r] = (float)(p.G * day[r]);
+                a[2][r] = (float)(p.G * daz[r]);
+            }
+            if (p.flags & NB_F_STORE_ACC) {
+                float4 *acc = static_cast<float4 *>(p.acc);
+#pragma unroll
+                for (int c = 0; c < 3; ++c)
+                    acc[(size_t)iq * 3 + c] = make_float4(a[c][0], a[c][1], a[c][2], a[c][3]);
+            }
+            if (p.flags & (NB_F_KICK2 | NB_F_KICK1_DRIFT)) {
+                float4 *vel = static_cast<float4 *>(p.vel);
+                float4 *qn = static_cast<float4 *>(p.q_next);
+                const float xin[3][4] = {{XI.x, XI.y, XI.z, XI.w},
+                                         {YI.x, YI.y, YI.z, YI.w},
+                                         {ZI.x, ZI.y, ZI.z, ZI.w}};
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const float4 V = vel[(size_t)iq * 3 + c];
+                    float v[4] = {V.x, V.y, V.z, V.w};
+                    float x[4];
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) {
+                        const bool real = (iq * 4u + r) < p.n_real;
+                        if (p.flags & NB_F_KICK2) v[r] = kick(v[r], a[c][r], dtf);
+                        if (p.flags & NB_F_KICK1_DRIFT) v[r] = kick(v[r], a[c][r], dtf);
+                        x[r] = (p.flags & NB_F_KICK1_DRIFT) ? drift(xin[c][r], v[r], dtf)
+                                                            : xin[c][r];
+                        if (!real) { v[r] = 0.f; x[r] = xin[c][r]; }
+                    }
+                    vel[(size_t)iq * 3 + c] = make_float4(v[0], v[1], v[2], v[3]);
+                    if (p.flags & NB_F_KICK1_DRIFT)
+                        qn[(size_t)iq * 4 + c] = make_float4(x[0], x[1], x[2], x[3]);
+                }
+            }
+        }
+    }
+}
+
+} // namespace
+
+// ------------------------------------------------------------------ host ----
+void finish_plan(DirectPlan *plan, int tune_flags)
+{
+    const unsigned long long total = (unsigned long long)plan->n_iblocks * plan->n_jtiles;
+    if (tune_flags & 2 /* NB_TUNE_NO_SPLIT */) plan->grid = plan->n_iblocks;
+    if ((unsigned long long)plan->grid > total) plan->grid = (unsigned)total;
+    if (plan->grid == 0) plan->grid = 1;
+    WorkSplit ws{total, plan->n_iblocks, plan->n_jtiles, plan->grid};
+    unsigned max_slots = 1;
+    for (unsigned ib = 0; ib < plan->n_iblocks; ++ib) {
+        const unsigned long long x0 = (unsigned long long)ib * plan->n_jtiles;
+        const unsigned s = ws.owner(x0 + plan->n_jtiles - 1) - ws.owner(x0) + 1;
+        if (s > max_slots) max_slots = s;
+    }
+    plan->max_slots = max_slots;
+    plan->workspace_bytes =
+        (size_t)plan->n_iblocks * max_slots * plan->slot_doubles * sizeof(double);
+    plan->counter_bytes = (size_t)plan->n_iblocks * sizeof(unsigned);
+}
+
+namespace {
+// Size classes.  i-block = NW*128 bodies, j-tile = TQ*4 bodies, MINB resident
+// CTAs per SM asked of ptxas (register cap).
+// tune_flags bits 8..11 = variant + 1 forces a class (A/B runs).
+struct VariantF32 {
+    int nw, tq, minb;
+};
+constexpr int kNumVariants = 3;
+constexpr VariantF32 kVariants[kNumVariants] = {
+    {7, 64, 2},  // 0 large : 2 x 8 warps per SM, <=128 regs
+    {3, 64, 4},  // 1 medium: 4 x 4 warps per SM
+    {1, 16, 8},  // 2 small : latency regime
+};
+
+template <int NW, int TQ, int MINB>
+cudaError_t launch_variant(const DirectPlan &plan, const StepParams &p, bool packed,
+                           cudaStream_t stream)
+{
+    if (packed)
+        direct_f32_kernel<NW, TQ, true, MINB><<<plan.grid, plan.block, 0, stream>>>(p);
+    else
+        direct_f32_kernel<NW, TQ, false, MINB><<<plan.grid, plan.block, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+
+template <int NW, int TQ, int MINB>
+int occupancy_variant(bool packed)
+{
+    int n = 0;
+    if (packed)
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+            &n, direct_f32_kernel<NW, TQ, true, MINB>, (NW + 1) * 32, 0);
+    else
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+            &n, direct_f32_kernel<NW, TQ, false, MINB>, (NW + 1) * 32, 0);
+    return n;
+}
+} // namespace
+
+cudaError_t plan_direct_f32(DirectPlan *plan, unsigned slice_units, unsigned n_units, int sm_count,
+                            int ctas_per_sm, int tune_flags)
+{
+    const unsigned slice_bodies = slice_units * 4u;
+    int v = 0;
+    if (slice_bodies < 16384u) v = 2;
+    else if (slice_bodies < 148u * 2048u) v = 1;
+    const int forced = (tune_flags >> 8) & 0xf;
+    if (forced >= 1 && forced <= kNumVariants) v = forced - 1;
+    const VariantF32 &k = kVariants[v];
+    plan->precision = 1;
+    plan->variant = v;
+    plan->units_per_iblock = (unsigned)k.nw * 32u;
+    plan->units_per_tile = (unsigned)k.tq;
+    plan->n_iblocks = (slice_units + plan->units_per_iblock - 1) / plan->units_per_iblock;
+    plan->n_jtiles = (n_units + plan->units_per_tile - 1) / plan->units_per_tile;
+    plan->block = (unsigned)(k.nw + 1) * 32u;
+    plan->slot_doubles = (size_t)plan->units_per_iblock * 12;
+    const bool packed = !(tune_flags & 1);
+    int occ = 0;
+    switch (v) {
+    case 0: occ = occupancy_variant<7, 64, 2>(packed); break;
+    case 1: occ = occupancy_variant<3, 64, 4>(packed); break;
+    default: occ = occupancy_variant<1, 16, 8>(packed); break;
+    }
+    cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) return err;
+    if (occ < 1) occ = 1;
+    int per_sm = ctas_per_sm > 0 ? ctas_per_sm : k.minb;
+    if (per_sm > occ) per_sm = occ;
+    plan->grid = (unsigned)(sm_count * per_sm);
+    finish_plan(plan, tune_flags);
+    return cudaSuccess;
+}
+
+cudaError_t launch_direct_f32(const DirectPlan &plan, StepParams p, int tune_flags,
+                              cudaStream_t stream)
+{
+    p.max_slots = plan.max_slots;
+    p.ws = WorkSplit{(unsigned long long)plan.n_iblocks * plan.n_jtiles, plan.n_iblocks,
+                     plan.n_jtiles, plan.grid};
+    const bool packed = !(tune_flags & 1);
+    switch (plan.variant) {
+    case 0: return launch_variant<7, 64, 2>(plan, p, packed, stream);
+    case 1: return launch_variant<3, 64, 4>(plan, p, packed, stream);
+    default: return launch_variant<1, 16, 8>(plan, p, packed, stream);
+    }
+}
+
+} // namespace nb

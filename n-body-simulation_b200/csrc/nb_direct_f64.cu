@@ -1,0 +1,288 @@
+// nb_direct_f64.cu -- the FP64 O(N^2) force + leapfrog kernel for sm_100a.
+//
+// Same structure as the FP32 kernel (nb_direct_f32.cu): TMA-fed mbarrier ring
+// of j-tiles, persistent grid over an evenly cut (i-block x j-tile) list,
+// last-arriver epilogue with the kick/drift fused in.  Differences:
+//   * the reference's precision (serial/exhaustive.c is FP64 throughout), so
+//     this is the kernel the parity tests hold to 1e-10 / 1e-12;
+//   * bodies are double4 {x,y,z,m} (32 B), two i-bodies per thread;
+//   * pow(r2, -1.5) (serial/exhaustive.c:173) becomes y^3 with y = r2^-1/2 from
+//     MUFU.RSQ64H (rsqrt.approx.ftz.f64, ~2^-22) refined by one cubically
+//     convergent step: e = 1 - r2*y0^2 ; y = y0 + y0*e*(1/2 + 3/8 e)
+//     (relative error ~ (5/16) e^3 < 2^-60), 5 DFMA-pipe operations;
+//   * accumulation is plain FP64 in j order inside a CTA's j-range; partial
+//     ranges are added in fixed slot order.
+// Per interaction: 3 DADD + 6 DFMA + 5 (rsqrt) + 3 DMUL = 17 FP64-pipe
+// operations + 1 MUFU.
+#include "nb_direct.cuh"
+
+namespace nb {
+namespace {
+
+constexpr int STAGES64 = 4;
+
+__device__ __forceinline__ void named_sync64(int id, int nthreads)
+{
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// m * (r2)^(-3/2)
+__device__ __forceinline__ double inv_r3_times_m(double r2, double m)
+{
+    const double y0 = rsqrt_approx_f64(r2);
+    const double t = r2 * y0;
+    const double e = fma(-t, y0, 1.0);
+    const double pe = fma(0.375, e, 0.5);
+    const double ye = y0 * e;
+    const double y = fma(ye, pe, y0);
+    const double y2 = y * y;
+    const double my = m * y;
+    return y2 * my;
+}
+
+// v += (a*dt)/2.0 and x += v*dt with the reference's roundings
+// (serial/exhaustive.c:221-232): no FMA contraction.
+__device__ __forceinline__ double kick64(double v, double a, double dt)
+{
+    return __dadd_rn(v, __dmul_rn(__dmul_rn(a, dt), 0.5));
+}
+__device__ __forceinline__ double drift64(double x, double v, double dt)
+{
+    return __dadd_rn(x, __dmul_rn(v, dt));
+}
+
+template <int NW, int TB, int MINB>
+__global__ void __launch_bounds__((NW + 1) * 32, MINB)
+    direct_f64_kernel(const StepParams p)
+{
+    constexpr int TPB = NW * 32;  // compute threads
+    constexpr int BPB = TPB * 2;  // bodies per i-block
+    __shared__ __align__(128) double4 tiles[STAGES64][TB];
+    __shared__ __align__(8) uint64_t full_bar[STAGES64];
+    __shared__ __align__(8) uint64_t empty_bar[STAGES64];
+    __shared__ unsigned s_last;
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const double4 *__restrict__ q = static_cast<const double4 *>(p.q_cur);
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES64; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], NW);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    const unsigned long long w0 = p.ws.bound(blockIdx.x);
+    const unsigned long long w1 = p.ws.bound(blockIdx.x + 1);
+    const unsigned n_jtiles = p.ws.n_jtiles;
+
+    if (warp == NW) {
+        if (lane == 0) {
+            unsigned stage = 0, phase = 0;
+            unsigned t = (unsigned)(w0 % n_jtiles);
+            for (unsigned long long w = w0; w < w1; ++w) {
+                mbar_wait(&empty_bar[stage], phase ^ 1u);
+                const unsigned first = t * TB;
+                const unsigned nb = min((unsigned)TB, p.n_units - first);
+                const unsigned bytes = nb * 32u;
+                mbar_arrive_expect_tx(&full_bar[stage], bytes);
+                tma_load_1d(&tiles[stage][0], q + first, bytes, &full_bar[stage]);
+                if (++stage == STAGES64) { stage = 0; phase ^= 1u; }
+                if (++t == n_jtiles) t = 0;
+            }
+        }
+        return;
+    }
+
+    const int tidc = threadIdx.x;
+    unsigned stage = 0, phase = 0;
+    unsigned long long w = w0;
+    while (w < w1) {
+        const unsigned ib = (unsigned)(w / n_jtiles);
+        const unsigned t0 = (unsigned)(w - (unsigned long long)ib * n_jtiles);
+        const unsigned cnt = (unsigned)min((unsigned long long)(n_jtiles - t0), w1 - w);
+        unsigned bi[2];
+        bool valid[2];
+        double xi[2], yi[2], zi[2];
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            bi[r] = p.i_begin + ib * BPB + r * TPB + tidc;
+            valid[r] = bi[r] < p.i_end;
+            const double4 b = q[valid[r] ? bi[r] : p.i_begin];
+            xi[r] = b.x; yi[r] = b.y; zi[r] = b.z;
+        }
+        double ax[2] = {0, 0}, ay[2] = {0, 0}, az[2] = {0, 0};
+
+        for (unsigned k = 0; k < cnt; ++k) {
+            const unsigned first = (t0 + k) * TB;
+            const int nb = (int)min((unsigned)TB, p.n_units - first);
+            mbar_wait(&full_bar[stage], phase);
+            const double4 *__restrict__ tile = &tiles[stage][0];
+#pragma unroll 4
+            for (int j = 0; j < nb; ++j) {
+                const double4 b = tile[j];
+#pragma unroll
+                for (int r = 0; r < 2; ++r) {
+                    const double dx = b.x - xi[r];
+                    const double dy = b.y - yi[r];
+                    const double dz = b.z - zi[r];
+                    double r2 = fma(dx, dx, p.eps2);
+                    r2 = fma(dy, dy, r2);
+                    r2 = fma(dz, dz, r2);
+                    const double s = inv_r3_times_m(r2, b.w);
+                    ax[r] = fma(dx, s, ax[r]);
+                    ay[r] = fma(dy, s, ay[r]);
+                    az[r] = fma(dz, s, az[r]);
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty_bar[stage]);
+            if (++stage == STAGES64) { stage = 0; phase ^= 1u; }
+        }
+        w += cnt;
+
+        bool do_epilogue = true;
+        if (cnt != n_jtiles) {
+            const unsigned long long x0 = (unsigned long long)ib * n_jtiles;
+            const unsigned c_first = p.ws.owner(x0);
+            const unsigned c_last = p.ws.owner(x0 + n_jtiles - 1);
+            const unsigned nslots = c_last - c_first + 1;
+            const unsigned slot = blockIdx.x - c_first;
+            double2 *ws = reinterpret_cast<double2 *>(p.workspace) +
+                          ((size_t)ib * p.max_slots) * (size_t)(TPB * 3);
+            double2 *mine = ws + (size_t)slot * (TPB * 3);
+            mine[0 * TPB + tidc] = make_double2(ax[0], ax[1]);
+            mine[1 * TPB + tidc] = make_double2(ay[0], ay[1]);
+            mine[2 * TPB + tidc] = make_double2(az[0], az[1]);
+            __threadfence();
+            named_sync64(1, TPB);
+            if (tidc == 0) {
+                const unsigned old = atomicAdd(&p.counters[ib], 1u);
+                const unsigned last = (old == nslots - 1);
+                if (last) p.counters[ib] = 0;
+                s_last = last;
+            }
+            named_sync64(1, TPB);
+            do_epilogue = (s_last != 0);
+            if (do_epilogue) {
+                __threadfence();
+                ax[0] = ax[1] = ay[0] = ay[1] = az[0] = az[1] = 0.0;
+                for (unsigned s = 0; s < nslots; ++s) {
+                    const double2 *src = ws + (size_t)s * (TPB * 3);
+                    double2 v;
+                    v = __ldcg(&src[0 * TPB + tidc]); ax[0] += v.x; ax[1] += v.y;
+                    v = __ldcg(&src[1 * TPB + tidc]); ay[0] += v.x; ay[1] += v.y;
+                    v = __ldcg(&src[2 * TPB + tidc]); az[0] += v.x; az[1] += v.y;
+                }
+            }
+            named_sync64(1, TPB);
+        }
+
+        if (do_epilogue) {
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+                if (!valid[r]) continue;
+                const unsigned b = bi[r];
+                const double a3[3] = {p.G * ax[r], p.G * ay[r], p.G * az[r]};
+                if (p.flags & NB_F_STORE_ACC)
+                    static_cast<double4 *>(p.acc)[b] = make_double4(a3[0], a3[1], a3[2], 0.0);
+                if (p.flags & (NB_F_KICK2 | NB_F_KICK1_DRIFT)) {
+                    double4 *vel = static_cast<double4 *>(p.vel);
+                    double4 V = vel[b];
+                    double v3[3] = {V.x, V.y, V.z};
+                    double x3[3] = {xi[r], yi[r], zi[r]};
+                    const bool real = b < p.n_real;
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        if (p.flags & NB_F_KICK2) v3[c] = kick64(v3[c], a3[c], p.dt);
+                        if (p.flags & NB_F_KICK1_DRIFT) {
+                            v3[c] = kick64(v3[c], a3[c], p.dt);
+                            x3[c] = drift64(x3[c], v3[c], p.dt);
+                        }
+                        if (!real) { v3[c] = 0.0; x3[c] = (c == 0 ? xi[r] : c == 1 ? yi[r] : zi[r]); }
+                    }
+                    vel[b] = make_double4(v3[0], v3[1], v3[2], 0.0);
+                    if (p.flags & NB_F_KICK1_DRIFT) {
+                        // mass rides along: q_next[b].w was set at upload and never changes
+                        double *qn = reinterpret_cast<double *>(static_cast<double4 *>(p.q_next) + b);
+                        qn[0] = x3[0]; qn[1] = x3[1]; qn[2] = x3[2];
+                    }
+                }
+            }
+        }
+    }
+}
+
+struct VariantF64 {
+    int nw, tb, minb;
+};
+constexpr int kNumVariants64 = 3;
+constexpr VariantF64 kVariants64[kNumVariants64] = {
+    {7, 128, 2}, // large : i-block 448 bodies
+    {3, 128, 4}, // medium: i-block 192 bodies
+    {1, 32, 8},  // small : i-block 64 bodies
+};
+
+template <int NW, int TB, int MINB>
+int occupancy64()
+{
+    int n = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, direct_f64_kernel<NW, TB, MINB>,
+                                                  (NW + 1) * 32, 0);
+    return n;
+}
+} // namespace
+
+cudaError_t plan_direct_f64(DirectPlan *plan, unsigned slice_units, unsigned n_units, int sm_count,
+                            int ctas_per_sm, int tune_flags)
+{
+    int v = 0;
+    if (slice_units < 8192u) v = 2;
+    else if (slice_units < 148u * 896u) v = 1;
+    const int forced = (tune_flags >> 8) & 0xf;
+    if (forced >= 1 && forced <= kNumVariants64) v = forced - 1;
+    const VariantF64 &k = kVariants64[v];
+    plan->precision = 0;
+    plan->variant = v;
+    plan->units_per_iblock = (unsigned)k.nw * 64u;
+    plan->units_per_tile = (unsigned)k.tb;
+    plan->n_iblocks = (slice_units + plan->units_per_iblock - 1) / plan->units_per_iblock;
+    plan->n_jtiles = (n_units + plan->units_per_tile - 1) / plan->units_per_tile;
+    plan->block = (unsigned)(k.nw + 1) * 32u;
+    plan->slot_doubles = (size_t)k.nw * 32 * 6;
+    int occ = 0;
+    switch (v) {
+    case 0: occ = occupancy64<7, 128, 2>(); break;
+    case 1: occ = occupancy64<3, 128, 4>(); break;
+    default: occ = occupancy64<1, 32, 8>(); break;
+    }
+    cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) return err;
+    if (occ < 1) occ = 1;
+    int per_sm = ctas_per_sm > 0 ? ctas_per_sm : k.minb;
+    if (per_sm > occ) per_sm = occ;
+    plan->grid = (unsigned)(sm_count * per_sm);
+    finish_plan(plan, tune_flags);
+    return cudaSuccess;
+}
+
+cudaError_t launch_direct_f64(const DirectPlan &plan, StepParams p, int tune_flags,
+                              cudaStream_t stream)
+{
+    (void)tune_flags;
+    p.max_slots = plan.max_slots;
+    p.ws = WorkSplit{(unsigned long long)plan.n_iblocks * plan.n_jtiles, plan.n_iblocks,
+                     plan.n_jtiles, plan.grid};
+    switch (plan.variant) {
+    case 0: direct_f64_kernel<7, 128, 2><<<plan.grid, plan.block, 0, stream>>>(p); break;
+    case 1: direct_f64_kernel<3, 128, 4><<<plan.grid, plan.block, 0, stream>>>(p); break;
+    default: direct_f64_kernel<1, 32, 8><<<plan.grid, plan.block, 0, stream>>>(p); break;
+    }
+    return cudaGetLastError();
+}
+
+} // namespace nb

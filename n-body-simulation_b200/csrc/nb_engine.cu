@@ -1,0 +1,569 @@
+// nb_engine.cu -- C ABI of the engine (include/nbody_engine.h): state machine
+// of the fused leapfrog, device memory, multi-rank all-gather.
+//
+// Leapfrog fusion (reference loop: serial/exhaustive.c:206,218-250):
+//   reference step k -> k+1 :  v += a(x_k) dt/2 ; x_{k+1} = x_k + v dt ; v += a(x_{k+1}) dt/2
+// A launch cannot drift and then read everybody's new positions, so the force
+// launch at x_k carries kick2 of step k-1 and kick1+drift of step k:
+//   SYNCED_NOACC --[F,K1,D]--> MIDSTEP --[F,K2,K1,D]--> MIDSTEP ... --[F,K2,store a]--> SYNCED_ACC
+//   SYNCED_ACC   --[K1,D from stored a]--> MIDSTEP
+// n steps + a gather with velocities = n+1 force launches, the reference's count.
+#include <dlfcn.h>
+#include <new>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../../include/nbody_engine.h"
+#include "nb_aux.cuh"
+#include "nb_direct.cuh"
+
+using namespace nb;
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+void set_err(const char *what, const char *detail)
+{
+    snprintf(g_err, sizeof(g_err), "%s: %s", what, detail ? detail : "");
+}
+
+#define NB_CUDA(call)                                                  \
+    do {                                                               \
+        cudaError_t _e = (call);                                       \
+        if (_e != cudaSuccess) {                                       \
+            set_err(#call, cudaGetErrorString(_e));                    \
+            return _e == cudaErrorMemoryAllocation ? NB_E_NOMEM : NB_E_CUDA; \
+        }                                                              \
+    } while (0)
+
+// ---- NCCL, bound at run time (libnccl.so.2: torch's copy if already loaded,
+// else the system one).  Single-rank engines never touch it.
+struct nccl_id_t {
+    char internal[NB_COMM_ID_BYTES];
+};
+struct NcclApi {
+    void *lib = nullptr;
+    int (*GetUniqueId)(nccl_id_t *) = nullptr;
+    int (*CommInitRank)(void **, int, nccl_id_t, int) = nullptr;
+    int (*AllGather)(const void *, void *, size_t, int, void *, cudaStream_t) = nullptr;
+    int (*CommDestroy)(void *) = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+};
+NcclApi g_nccl;
+
+int load_nccl()
+{
+    if (g_nccl.lib) return NB_OK;
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    void *h = nullptr;
+    for (const char *nm : names)
+        if ((h = dlopen(nm, RTLD_NOW | RTLD_GLOBAL))) break;
+    if (!h) {
+        set_err("dlopen(libnccl.so.2)", dlerror());
+        return NB_E_COMM;
+    }
+    NcclApi a;
+    a.lib = h;
+    a.GetUniqueId = (int (*)(nccl_id_t *))dlsym(h, "ncclGetUniqueId");
+    a.CommInitRank = (int (*)(void **, int, nccl_id_t, int))dlsym(h, "ncclCommInitRank");
+    a.AllGather = (int (*)(const void *, void *, size_t, int, void *, cudaStream_t))dlsym(
+        h, "ncclAllGather");
+    a.CommDestroy = (int (*)(void *))dlsym(h, "ncclCommDestroy");
+    a.GetErrorString = (const char *(*)(int))dlsym(h, "ncclGetErrorString");
+    if (!a.GetUniqueId || !a.CommInitRank || !a.AllGather || !a.CommDestroy) {
+        set_err("dlsym(nccl)", "missing symbol");
+        return NB_E_COMM;
+    }
+    g_nccl = a;
+    return NB_OK;
+}
+
+#define NB_NCCL(call)                                                               \
+    do {                                                                            \
+        int _r = (call);                                                            \
+        if (_r != 0) {                                                              \
+            set_err(#call, g_nccl.GetErrorString ? g_nccl.GetErrorString(_r) : "nccl error"); \
+            return NB_E_COMM;                                                       \
+        }                                                                           \
+    } while (0)
+
+enum State { SYNCED_NOACC = 0, SYNCED_ACC = 1, MIDSTEP = 2 };
+
+} // namespace
+
+struct nb_engine {
+    nb_config cfg;
+    size_t n = 0;          // real bodies
+    unsigned unit_bodies = 1; // 4 (FP32 quads) or 1 (FP64)
+    size_t unit_bytes = 0;    // bytes of one position unit
+    size_t vel_unit_bytes = 0;
+    unsigned n_units = 0;     // padded j extent in units
+    unsigned slice_units = 0; // units per rank
+    unsigned i_begin = 0, i_end = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_step0 = nullptr, ev_step1 = nullptr, ev_f0 = nullptr, ev_f1 = nullptr;
+    bool have_step_ev = false, have_force_ev = false;
+    void *q[2] = {nullptr, nullptr};
+    int cur = 0;
+    void *vel = nullptr, *acc = nullptr;
+    double *workspace = nullptr;
+    unsigned *counters = nullptr;
+    double *stage_pos = nullptr, *stage_vel = nullptr; // host-packing staging, n*4 / n*3 doubles
+    double *energy_part = nullptr;
+    DirectPlan plan;
+    State state = SYNCED_NOACC;
+    void *comm = nullptr;
+    bool vel_complete = true; // world > 1: do all ranks hold all velocities?
+    nb_stats st;
+};
+
+namespace {
+
+int set_device(nb_engine *e)
+{
+    NB_CUDA(cudaSetDevice(e->cfg.device));
+    return NB_OK;
+}
+
+int all_gather_units(nb_engine *e, void *buf, size_t unit_bytes)
+{
+    if (e->cfg.world <= 1) return NB_OK;
+    const size_t bytes = (size_t)e->slice_units * unit_bytes;
+    const char *send = (const char *)buf + (size_t)e->cfg.rank * bytes;
+    NB_NCCL(g_nccl.AllGather(send, buf, bytes, /*ncclInt8*/ 0, e->comm, e->stream));
+    return NB_OK;
+}
+
+// One force launch with the given epilogue flags.  Positions move iff
+// NB_F_KICK1_DRIFT: then the own slice of q[next] is written, all-gathered
+// and the buffers swap.
+int launch_force(nb_engine *e, unsigned flags)
+{
+    StepParams p;
+    memset(&p, 0, sizeof(p));
+    p.q_cur = e->q[e->cur];
+    p.q_next = e->q[e->cur ^ 1];
+    p.vel = e->vel;
+    p.acc = e->acc;
+    p.workspace = e->workspace;
+    p.counters = e->counters;
+    p.n_real = (unsigned)e->n;
+    p.n_units = e->n_units;
+    p.i_begin = e->i_begin;
+    p.i_end = e->i_end;
+    p.flags = flags;
+    p.dt = e->cfg.dt;
+    p.eps2 = e->cfg.eps2;
+    p.G = e->cfg.G;
+    NB_CUDA(cudaEventRecord(e->ev_f0, e->stream));
+    if (e->cfg.precision == NB_PREC_FP32)
+        NB_CUDA(launch_direct_f32(e->plan, p, e->cfg.tune_flags, e->stream));
+    else
+        NB_CUDA(launch_direct_f64(e->plan, p, e->cfg.tune_flags, e->stream));
+    NB_CUDA(cudaEventRecord(e->ev_f1, e->stream));
+    e->have_force_ev = true;
+    e->st.force_launches++;
+    e->st.kernel_launches++;
+    e->st.interactions += (unsigned long long)(e->i_end - e->i_begin) * e->unit_bodies *
+                          (unsigned long long)e->n_units * e->unit_bodies;
+    if (flags & (NB_F_KICK2 | NB_F_KICK1_DRIFT)) e->vel_complete = (e->cfg.world <= 1);
+    if (flags & NB_F_KICK1_DRIFT) {
+        int rc = all_gather_units(e, e->q[e->cur ^ 1], e->unit_bytes);
+        if (rc) return rc;
+        e->cur ^= 1;
+    }
+    return NB_OK;
+}
+
+int close_step(nb_engine *e)
+{
+    if (e->state != MIDSTEP) return NB_OK;
+    int rc = launch_force(e, NB_F_KICK2 | NB_F_STORE_ACC);
+    if (rc) return rc;
+    e->state = SYNCED_ACC;
+    return NB_OK;
+}
+
+int ensure_vel_complete(nb_engine *e)
+{
+    if (e->vel_complete) return NB_OK;
+    int rc = all_gather_units(e, e->vel, e->vel_unit_bytes);
+    if (rc) return rc;
+    e->vel_complete = true;
+    return NB_OK;
+}
+
+int upload(nb_engine *e, const double *pos, const double *vel)
+{
+    const size_t n = e->n;
+    if (n) {
+        NB_CUDA(cudaMemcpyAsync(e->stage_pos, pos, n * 4 * sizeof(double), cudaMemcpyHostToDevice,
+                                e->stream));
+        if (vel)
+            NB_CUDA(cudaMemcpyAsync(e->stage_vel, vel, n * 3 * sizeof(double),
+                                    cudaMemcpyHostToDevice, e->stream));
+    }
+    NB_CUDA(pack_bodies(e->cfg.precision, e->stage_pos, vel ? e->stage_vel : nullptr, (unsigned)n,
+                        e->n_units, e->q[0], e->q[1], e->vel, e->stream));
+    e->st.kernel_launches++;
+    e->cur = 0;
+    e->state = SYNCED_NOACC;
+    e->vel_complete = true;
+    e->st.steps_done = 0;
+    return NB_OK;
+}
+
+} // namespace
+
+// =============================================================== C ABI =====
+extern "C" {
+
+void nb_config_default(nb_config *cfg)
+{
+    memset(cfg, 0, sizeof(*cfg));
+    cfg->precision = NB_PREC_FP64;
+    cfg->algorithm = NB_ALGO_DIRECT;
+    cfg->dt = (double)0.01f;
+    cfg->eps2 = 0.01;
+    cfg->G = 1.0;
+    cfg->theta = 0.5;
+    cfg->device = 0;
+    cfg->rank = 0;
+    cfg->world = 1;
+}
+
+int nb_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+const char *nb_version(void) { return "nbody_b200 0.1 (sm_100a)"; }
+
+const char *nb_last_error(void) { return g_err; }
+
+const char *nb_strerror(int code)
+{
+    switch (code) {
+    case NB_OK: return "ok";
+    case NB_E_INVALID: return "invalid argument";
+    case NB_E_CUDA: return "CUDA error";
+    case NB_E_NOMEM: return "out of memory";
+    case NB_E_COMM: return "communicator (NCCL) error";
+    case NB_E_NODEVICE: return "no CUDA device (this engine has no CPU fallback)";
+    case NB_E_STATE: return "call not valid in this state";
+    default: return "unknown error";
+    }
+}
+
+int nb_comm_id(void *id_out, size_t bytes)
+{
+    if (!id_out || bytes < NB_COMM_ID_BYTES) return NB_E_INVALID;
+    int rc = load_nccl();
+    if (rc) return rc;
+    nccl_id_t id;
+    NB_NCCL(g_nccl.GetUniqueId(&id));
+    memcpy(id_out, &id, NB_COMM_ID_BYTES);
+    return NB_OK;
+}
+
+void nb_free(nb_engine *e)
+{
+    if (!e) return;
+    cudaSetDevice(e->cfg.device);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
+    void *bufs[] = {e->q[0], e->q[1], e->vel, e->acc, e->workspace, e->counters,
+                    e->stage_pos, e->stage_vel, e->energy_part};
+    for (void *b : bufs)
+        if (b) cudaFree(b);
+    cudaEvent_t evs[] = {e->ev_step0, e->ev_step1, e->ev_f0, e->ev_f1};
+    for (cudaEvent_t ev : evs)
+        if (ev) cudaEventDestroy(ev);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+static int init_impl(nb_engine *e, const double *pos, const double *vel)
+{
+    const nb_config &c = e->cfg;
+    int rc = set_device(e);
+    if (rc) return rc;
+    cudaDeviceProp prop;
+    NB_CUDA(cudaGetDeviceProperties(&prop, c.device));
+    if (prop.major < 10) {
+        set_err("nb_init", "device is not sm_100 class; this library carries sm_100a code only");
+        return NB_E_NODEVICE;
+    }
+    e->sm_count = prop.multiProcessorCount;
+    NB_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+    NB_CUDA(cudaEventCreate(&e->ev_step0));
+    NB_CUDA(cudaEventCreate(&e->ev_step1));
+    NB_CUDA(cudaEventCreate(&e->ev_f0));
+    NB_CUDA(cudaEventCreate(&e->ev_f1));
+
+    const bool f32 = c.precision == NB_PREC_FP32;
+    e->unit_bodies = f32 ? 4u : 1u;
+    e->unit_bytes = f32 ? 64 : 32;
+    e->vel_unit_bytes = f32 ? 48 : 32;
+    // slices: equal unit counts per rank (in-place all-gather), multiple of 32 units
+    const size_t units = (e->n + e->unit_bodies - 1) / e->unit_bodies;
+    size_t per = (units + c.world - 1) / c.world;
+    if (c.world > 1) per = (per + 31) / 32 * 32;
+    if (per == 0) per = 1;
+    if (per * (size_t)c.world * e->unit_bodies > 0x7fffffffu) {
+        set_err("nb_init", "too many bodies for 32-bit indices");
+        return NB_E_INVALID;
+    }
+    e->slice_units = (unsigned)per;
+    e->n_units = (unsigned)(per * c.world);
+    e->i_begin = (unsigned)(per * c.rank);
+    e->i_end = (unsigned)(per * (c.rank + 1));
+    // units past the last real body need no force evaluation
+    const unsigned real_units = (unsigned)units;
+    if (e->i_end > real_units) e->i_end = real_units > e->i_begin ? real_units : e->i_begin;
+
+    const unsigned my_units = e->i_end - e->i_begin;
+    cudaError_t pe = f32 ? plan_direct_f32(&e->plan, my_units ? my_units : 1, e->n_units,
+                                           e->sm_count, c.tune_ctas_per_sm, c.tune_flags)
+                         : plan_direct_f64(&e->plan, my_units ? my_units : 1, e->n_units,
+                                           e->sm_count, c.tune_ctas_per_sm, c.tune_flags);
+    NB_CUDA(pe);
+
+    const size_t qbytes = (size_t)e->n_units * e->unit_bytes;
+    const size_t vbytes = (size_t)e->n_units * e->vel_unit_bytes;
+    NB_CUDA(cudaMalloc(&e->q[0], qbytes));
+    NB_CUDA(cudaMalloc(&e->q[1], qbytes));
+    NB_CUDA(cudaMalloc(&e->vel, vbytes));
+    NB_CUDA(cudaMalloc(&e->acc, vbytes));
+    NB_CUDA(cudaMemsetAsync(e->acc, 0, vbytes, e->stream));
+    NB_CUDA(cudaMalloc(&e->workspace, e->plan.workspace_bytes ? e->plan.workspace_bytes : 16));
+    NB_CUDA(cudaMalloc(&e->counters, e->plan.counter_bytes ? e->plan.counter_bytes : 16));
+    NB_CUDA(cudaMemsetAsync(e->counters, 0, e->plan.counter_bytes ? e->plan.counter_bytes : 16,
+                            e->stream));
+    NB_CUDA(cudaMalloc(&e->stage_pos, (e->n ? e->n : 1) * 4 * sizeof(double)));
+    NB_CUDA(cudaMalloc(&e->stage_vel, (e->n ? e->n : 1) * 3 * sizeof(double)));
+    NB_CUDA(cudaMalloc(&e->energy_part, (size_t)(energy_blocks((unsigned)e->n) + 1) * 2 * sizeof(double)));
+
+    if (c.world > 1) {
+        rc = load_nccl();
+        if (rc) return rc;
+        if (!c.comm_id) {
+            set_err("nb_init", "world > 1 needs cfg.comm_id from nb_comm_id()");
+            return NB_E_INVALID;
+        }
+        nccl_id_t id;
+        memcpy(&id, c.comm_id, NB_COMM_ID_BYTES);
+        NB_NCCL(g_nccl.CommInitRank(&e->comm, c.world, id, c.rank));
+    }
+    e->cfg.comm_id = nullptr; // caller's buffer is not kept
+
+    rc = upload(e, pos, vel);
+    if (rc) return rc;
+    NB_CUDA(cudaStreamSynchronize(e->stream));
+    e->st.n = e->n;
+    e->st.n_padded = (size_t)e->n_units * e->unit_bodies;
+    e->st.slice_begin = (size_t)e->i_begin * e->unit_bodies;
+    e->st.slice_end = (size_t)e->i_end * e->unit_bodies;
+    if (e->st.slice_end > e->n) e->st.slice_end = e->n;
+    if (e->st.slice_begin > e->n) e->st.slice_begin = e->n;
+    e->st.grid = (int)e->plan.grid;
+    e->st.block = (int)e->plan.block;
+    return NB_OK;
+}
+
+int nb_init(nb_engine **out, const nb_config *cfg, size_t n, const double *pos_xyzm,
+            const double *vel_xyz)
+{
+    if (!out || !cfg) return NB_E_INVALID;
+    *out = nullptr;
+    if ((n && !pos_xyzm) || cfg->world < 1 || cfg->rank < 0 || cfg->rank >= cfg->world ||
+        (cfg->precision != NB_PREC_FP64 && cfg->precision != NB_PREC_FP32) ||
+        !(cfg->dt == cfg->dt) || cfg->eps2 < 0) {
+        set_err("nb_init", "bad configuration");
+        return NB_E_INVALID;
+    }
+    if (cfg->algorithm != NB_ALGO_DIRECT) {
+        set_err("nb_init", "algorithm not available in this build");
+        return NB_E_INVALID;
+    }
+    int ndev = nb_device_count();
+    if (ndev <= 0 || cfg->device < 0 || cfg->device >= ndev) {
+        set_err("nb_init", "no usable CUDA device; the engine has no CPU fallback");
+        return NB_E_NODEVICE;
+    }
+    nb_engine *e = new (std::nothrow) nb_engine();
+    if (!e) return NB_E_NOMEM;
+    memset(&e->st, 0, sizeof(e->st));
+    e->cfg = *cfg;
+    e->n = n;
+    int rc = init_impl(e, pos_xyzm, vel_xyz);
+    if (rc) {
+        nb_free(e);
+        return rc;
+    }
+    *out = e;
+    return NB_OK;
+}
+
+int nb_upload(nb_engine *e, const double *pos_xyzm, const double *vel_xyz)
+{
+    if (!e || (e->n && !pos_xyzm)) return NB_E_INVALID;
+    int rc = set_device(e);
+    if (rc) return rc;
+    rc = upload(e, pos_xyzm, vel_xyz);
+    if (rc) return rc;
+    NB_CUDA(cudaStreamSynchronize(e->stream));
+    return NB_OK;
+}
+
+int nb_step(nb_engine *e, int n_steps)
+{
+    if (!e || n_steps < 0) return NB_E_INVALID;
+    int rc = set_device(e);
+    if (rc) return rc;
+    NB_CUDA(cudaEventRecord(e->ev_step0, e->stream));
+    for (int s = 0; s < n_steps; ++s) {
+        if (e->state == SYNCED_ACC) {
+            NB_CUDA(kickdrift(e->cfg.precision, e->q[e->cur], e->q[e->cur ^ 1], e->vel, e->acc,
+                              e->i_begin, e->i_end, (unsigned)e->n, e->cfg.dt, e->stream));
+            e->st.kernel_launches++;
+            e->vel_complete = (e->cfg.world <= 1);
+            rc = all_gather_units(e, e->q[e->cur ^ 1], e->unit_bytes);
+            if (rc) return rc;
+            e->cur ^= 1;
+        } else if (e->state == SYNCED_NOACC) {
+            rc = launch_force(e, NB_F_KICK1_DRIFT);
+            if (rc) return rc;
+        } else {
+            rc = launch_force(e, NB_F_KICK2 | NB_F_KICK1_DRIFT);
+            if (rc) return rc;
+        }
+        e->state = MIDSTEP;
+        e->st.steps_done++;
+    }
+    NB_CUDA(cudaEventRecord(e->ev_step1, e->stream));
+    e->have_step_ev = true;
+    return NB_OK;
+}
+
+int nb_sync(nb_engine *e)
+{
+    if (!e) return NB_E_INVALID;
+    int rc = set_device(e);
+    if (rc) return rc;
+    NB_CUDA(cudaStreamSynchronize(e->stream));
+    return NB_OK;
+}
+
+int nb_gather(nb_engine *e, double *pos_xyzm, double *vel_xyz)
+{
+    if (!e) return NB_E_INVALID;
+    int rc = set_device(e);
+    if (rc) return rc;
+    const unsigned n = (unsigned)e->n;
+    if (vel_xyz) {
+        rc = close_step(e);
+        if (rc) return rc;
+        rc = ensure_vel_complete(e);
+        if (rc) return rc;
+        NB_CUDA(unpack_bodies(e->cfg.precision, e->vel, n, 3, e->stage_vel, e->stream));
+        e->st.kernel_launches++;
+        if (n)
+            NB_CUDA(cudaMemcpyAsync(vel_xyz, e->stage_vel, (size_t)n * 3 * sizeof(double),
+                                    cudaMemcpyDeviceToHost, e->stream));
+    }
+    if (pos_xyzm) {
+        NB_CUDA(unpack_bodies(e->cfg.precision, e->q[e->cur], n, 4, e->stage_pos, e->stream));
+        e->st.kernel_launches++;
+        if (n)
+            NB_CUDA(cudaMemcpyAsync(pos_xyzm, e->stage_pos, (size_t)n * 4 * sizeof(double),
+                                    cudaMemcpyDeviceToHost, e->stream));
+    }
+    NB_CUDA(cudaStreamSynchronize(e->stream));
+    return NB_OK;
+}
+
+int nb_accelerations(nb_engine *e, double *acc_xyz)
+{
+    if (!e || !acc_xyz) return NB_E_INVALID;
+    int rc = set_device(e);
+    if (rc) return rc;
+    if (e->state == MIDSTEP) {
+        rc = close_step(e);
+    } else if (e->state == SYNCED_NOACC) {
+        rc = launch_force(e, NB_F_STORE_ACC);
+        if (!rc) e->state = SYNCED_ACC;
+    }
+    if (rc) return rc;
+    rc = all_gather_units(e, e->acc, e->vel_unit_bytes);
+    if (rc) return rc;
+    const unsigned n = (unsigned)e->n;
+    NB_CUDA(unpack_bodies(e->cfg.precision, e->acc, n, 3, e->stage_vel, e->stream));
+    e->st.kernel_launches++;
+    if (n)
+        NB_CUDA(cudaMemcpyAsync(acc_xyz, e->stage_vel, (size_t)n * 3 * sizeof(double),
+                                cudaMemcpyDeviceToHost, e->stream));
+    NB_CUDA(cudaStreamSynchronize(e->stream));
+    return NB_OK;
+}
+
+int nb_energy(nb_engine *e, double *KE, double *PE)
+{
+    if (!e || !KE || !PE) return NB_E_INVALID;
+    int rc = set_device(e);
+    if (rc) return rc;
+    rc = close_step(e);
+    if (rc) return rc;
+    rc = ensure_vel_complete(e);
+    if (rc) return rc;
+    const unsigned n = (unsigned)e->n;
+    NB_CUDA(unpack_bodies(e->cfg.precision, e->vel, n, 3, e->stage_vel, e->stream));
+    NB_CUDA(unpack_bodies(e->cfg.precision, e->q[e->cur], n, 4, e->stage_pos, e->stream));
+    NB_CUDA(energy_partials(e->stage_pos, e->stage_vel, n, e->energy_part, e->stream));
+    e->st.kernel_launches += 3;
+    const unsigned nb = energy_blocks(n);
+    double *h = (double *)malloc((size_t)(nb + 1) * 2 * sizeof(double));
+    if (!h) return NB_E_NOMEM;
+    if (nb)
+        NB_CUDA(cudaMemcpyAsync(h, e->energy_part, (size_t)nb * 2 * sizeof(double),
+                                cudaMemcpyDeviceToHost, e->stream));
+    NB_CUDA(cudaStreamSynchronize(e->stream));
+    double ke = 0, pe = 0;
+    for (unsigned b = 0; b < nb; ++b) {
+        ke += h[2 * b];
+        pe += h[2 * b + 1];
+    }
+    free(h);
+    *KE = 0.5 * ke;
+    *PE = -e->cfg.G * pe;
+    return NB_OK;
+}
+
+int nb_get_stats(nb_engine *e, nb_stats *out)
+{
+    if (!e || !out) return NB_E_INVALID;
+    int rc = set_device(e);
+    if (rc) return rc;
+    NB_CUDA(cudaStreamSynchronize(e->stream));
+    float ms = 0.f;
+    if (e->have_step_ev) {
+        NB_CUDA(cudaEventElapsedTime(&ms, e->ev_step0, e->ev_step1));
+        e->st.last_step_ms = ms;
+    }
+    if (e->have_force_ev) {
+        NB_CUDA(cudaEventElapsedTime(&ms, e->ev_f0, e->ev_f1));
+        e->st.last_force_ms = ms;
+    }
+    *out = e->st;
+    return NB_OK;
+}
+
+} // extern "C"
