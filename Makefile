@@ -5,7 +5,7 @@ CSRC := $(PKG)/csrc
 HOST := $(PKG)/host
 NVCC ?= nvcc
 CC := gcc
-NVFLAGS := -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC
+NVFLAGS := --cudart static -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC
 LIB := $(PKG)/libnbody_b200.so
 BIN := $(PKG)/bin
 CU := $(CSRC)/nb_engine.cu $(CSRC)/nb_direct_f32.cu $(CSRC)/nb_direct_f64.cu $(CSRC)/nb_aux.cu

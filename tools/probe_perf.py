@@ -1,0 +1,61 @@
+#!/usr/bin/env python
+"""Kernel timing probe (GPU box): interactions/s of the direct-sum step for a list of
+configurations.  Device time comes from the engine's own CUDA events (nb_get_stats).
+    python tools/probe_perf.py fp32:1000000 fp32:1000000:scalar fp64:100000 ...
+Spec: prec:N[:opt[,opt]]  opts: scalar, nosplit, ctas=K, variant=V, steps=S
+"""
+import json
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests"))
+from conftest import load_package  # noqa: E402
+
+nb = load_package()
+
+
+def run(spec):
+    parts = spec.split(":")
+    prec = nb.PREC_FP32 if parts[0] == "fp32" else nb.PREC_FP64
+    n = int(parts[1])
+    opts = parts[2].split(",") if len(parts) > 2 else []
+    flags, ctas, steps = 0, 0, 3
+    for o in opts:
+        if o == "scalar":
+            flags |= nb.TUNE_SCALAR_FP32
+        elif o == "nosplit":
+            flags |= nb.TUNE_NO_SPLIT
+        elif o.startswith("ctas="):
+            ctas = int(o[5:])
+        elif o.startswith("variant="):
+            flags |= int(o[8:]) << 8
+        elif o.startswith("steps="):
+            steps = int(o[6:])
+    rng = np.random.default_rng(17)
+    pm = np.concatenate([rng.standard_normal((n, 3)), np.full((n, 1), 1.0 / n)], axis=1)
+    vel = np.zeros((n, 3))
+    with nb.Engine(pm, vel, precision=prec, ctas_per_sm=ctas, tune_flags=flags) as e:
+        e.step(2)  # warm-up
+        e.sync()
+        times = []
+        for _ in range(steps):
+            e.step(1)
+            st = e.stats()
+            times.append(st.last_force_ms)
+        st = e.stats()
+        best, med = min(times), float(np.median(times))
+        out = {"spec": spec, "n": n, "grid": st.grid, "block": st.block,
+               "force_ms_min": best, "force_ms_med": med,
+               "interactions_per_s": n * float(st.n_padded) / (med * 1e-3),
+               "frac_fp32_roofline_20flop_1965MHz": n * float(st.n_padded) / (med * 1e-3) / 3.72e12}
+    print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    for s in sys.argv[1:]:
+        try:
+            run(s)
+        except Exception as ex:  # keep going: this is a probe
+            print(json.dumps({"spec": s, "error": str(ex)}), flush=True)
