@@ -6,9 +6,11 @@
 //   * bodies live in HBM as 64-byte quads {X4,Y4,Z4,M4}; a thread owns one quad
 //     = a register block of 4 i-bodies (3 x 128-bit loads);
 //   * j-bodies stream through a 4-stage shared-memory ring filled by 1-D bulk
-//     async copies (TMA, SASS UBLKCP) from a dedicated producer warp and handed
-//     over with mbarriers; every compute warp reads a j-quad with four
-//     broadcast LDS.128;
+//     async copies (TMA, SASS UBLKCP) and handed over with mbarriers; the copy
+//     for tile k+2 is issued by one thread at the top of tile k (a dedicated
+//     producer warp would leave one of the four SM sub-partitions with fewer
+//     compute warps: measured 12 % loss, profiles/r1_notes.md); every warp
+//     reads a j-quad with four broadcast LDS.128;
 //   * the inner loop works on PAIRS of j-bodies with the sm_100 packed FP32
 //     instructions (FADD2/FFMA2/FMUL2): per 2 interactions 3 FADD2 + 6 FFMA2 +
 //     3 FMUL2 + 2 MUFU.RSQ, i.e. 12 FMA-pipe lane-operations and one MUFU per
@@ -101,7 +103,7 @@ __device__ __forceinline__ float drift(float x, float v, float dt)
 }
 
 template <int NW, int TQ, bool PACKED, int MINB>
-__global__ void __launch_bounds__((NW + 1) * 32, MINB)
+__global__ void __launch_bounds__(NW * 32, MINB)
     direct_f32_kernel(const StepParams p)
 {
     constexpr int QPB = NW * 32; // quads (threads) per i-block
@@ -113,7 +115,6 @@ __global__ void __launch_bounds__((NW + 1) * 32, MINB)
     // tile) so the inner loop keeps its registers for the 4x2 interaction block.
     __shared__ double dacc[12][QPB];
 
-    const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const float4 *__restrict__ q = static_cast<const float4 *>(p.q_cur);
 
@@ -131,31 +132,29 @@ __global__ void __launch_bounds__((NW + 1) * 32, MINB)
     const unsigned long long w1 = p.ws.bound(blockIdx.x + 1);
     const unsigned n_jtiles = p.ws.n_jtiles;
 
-    if (warp == NW) {
-        // ---------------- producer warp: one lane feeds the ring ----------------
-        if (lane == 0) {
-            unsigned stage = 0, phase = 0;
-            unsigned t = (unsigned)(w0 % n_jtiles);
-            for (unsigned long long w = w0; w < w1; ++w) {
-                mbar_wait(&empty_bar[stage], phase ^ 1u);
-                const unsigned first = t * TQ;
-                const unsigned nq = min((unsigned)TQ, p.n_units - first);
-                const unsigned bytes = nq * 64u;
-                mbar_arrive_expect_tx(&full_bar[stage], bytes);
-                tma_load_1d(&tiles[stage][0], q + (size_t)first * 4, bytes, &full_bar[stage]);
-                if (++stage == STAGES) { stage = 0; phase ^= 1u; }
-                if (++t == n_jtiles) t = 0;
-            }
-        }
-        return;
-    }
+    // -------- j-tile ring: tile k of this CTA's list lives in stage k % STAGES ----
+    // Thread 0 issues the copy of tile k + AHEAD at the top of tile k, into the
+    // stage all warps released two tiles ago, so it never waits on a laggard.
+    constexpr unsigned AHEAD = STAGES - 2;
+    const unsigned n_tiles = (unsigned)(w1 - w0);
+    const unsigned tile0 = (unsigned)(w0 % n_jtiles);
+    auto issue_tile = [&](unsigned k) {
+        const unsigned s = k % STAGES;
+        if (k >= STAGES) mbar_wait(&empty_bar[s], ((k / STAGES) - 1u) & 1u);
+        const unsigned first = ((tile0 + k) % n_jtiles) * TQ;
+        const unsigned nq = min((unsigned)TQ, p.n_units - first);
+        const unsigned bytes = nq * 64u;
+        mbar_arrive_expect_tx(&full_bar[s], bytes);
+        tma_load_1d(&tiles[s][0], q + (size_t)first * 4, bytes, &full_bar[s]);
+    };
+    if (threadIdx.x == 0)
+        for (unsigned k = 0; k < AHEAD && k < n_tiles; ++k) issue_tile(k);
 
-    // -------------------------- compute warps -----------------------------------
     const int tidc = threadIdx.x; // 0 .. QPB-1
     const float dtf = (float)p.dt;
     const float e2s = (float)p.eps2;
     const float2 e2 = make_float2(e2s, e2s);
-    unsigned stage = 0, phase = 0;
+    unsigned stage = 0, phase = 0, kt = 0;
 
     unsigned long long w = w0;
     while (w < w1) {
@@ -179,6 +178,8 @@ __global__ void __launch_bounds__((NW + 1) * 32, MINB)
 #pragma unroll
             for (int r = 0; r < 4; ++r) ax[r] = ay[r] = az[r] = make_float2(0.f, 0.f);
 
+            if (threadIdx.x == 0 && kt + AHEAD < n_tiles) issue_tile(kt + AHEAD);
+            ++kt;
             mbar_wait(&full_bar[stage], phase);
             const float4 *__restrict__ tile = &tiles[stage][0];
 #pragma unroll 2
@@ -338,8 +339,8 @@ struct VariantF32 {
 };
 constexpr int kNumVariants = 3;
 constexpr VariantF32 kVariants[kNumVariants] = {
-    {7, 64, 2},  // 0 large : 2 x 8 warps per SM, <=128 regs
-    {3, 64, 4},  // 1 medium: 4 x 4 warps per SM
+    {8, 64, 2},  // 0 large : 2 x 8 warps per SM, <=128 regs
+    {4, 64, 4},  // 1 medium: 4 x 4 warps per SM
     {1, 16, 8},  // 2 small : latency regime
 };
 
@@ -360,10 +361,10 @@ int occupancy_variant(bool packed)
     int n = 0;
     if (packed)
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(
-            &n, direct_f32_kernel<NW, TQ, true, MINB>, (NW + 1) * 32, 0);
+            &n, direct_f32_kernel<NW, TQ, true, MINB>, NW * 32, 0);
     else
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(
-            &n, direct_f32_kernel<NW, TQ, false, MINB>, (NW + 1) * 32, 0);
+            &n, direct_f32_kernel<NW, TQ, false, MINB>, NW * 32, 0);
     return n;
 }
 } // namespace
@@ -384,13 +385,13 @@ cudaError_t plan_direct_f32(DirectPlan *plan, unsigned slice_units, unsigned n_u
     plan->units_per_tile = (unsigned)k.tq;
     plan->n_iblocks = (slice_units + plan->units_per_iblock - 1) / plan->units_per_iblock;
     plan->n_jtiles = (n_units + plan->units_per_tile - 1) / plan->units_per_tile;
-    plan->block = (unsigned)(k.nw + 1) * 32u;
+    plan->block = (unsigned)k.nw * 32u;
     plan->slot_doubles = (size_t)plan->units_per_iblock * 12;
     const bool packed = !(tune_flags & 1);
     int occ = 0;
     switch (v) {
-    case 0: occ = occupancy_variant<7, 64, 2>(packed); break;
-    case 1: occ = occupancy_variant<3, 64, 4>(packed); break;
+    case 0: occ = occupancy_variant<8, 64, 2>(packed); break;
+    case 1: occ = occupancy_variant<4, 64, 4>(packed); break;
     default: occ = occupancy_variant<1, 16, 8>(packed); break;
     }
     cudaError_t err = cudaGetLastError();
@@ -411,8 +412,8 @@ cudaError_t launch_direct_f32(const DirectPlan &plan, StepParams p, int tune_fla
                      plan.n_jtiles, plan.grid};
     const bool packed = !(tune_flags & 1);
     switch (plan.variant) {
-    case 0: return launch_variant<7, 64, 2>(plan, p, packed, stream);
-    case 1: return launch_variant<3, 64, 4>(plan, p, packed, stream);
+    case 0: return launch_variant<8, 64, 2>(plan, p, packed, stream);
+    case 1: return launch_variant<4, 64, 4>(plan, p, packed, stream);
     default: return launch_variant<1, 16, 8>(plan, p, packed, stream);
     }
 }

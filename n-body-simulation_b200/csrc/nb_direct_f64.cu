@@ -6,14 +6,16 @@
 //   * the reference's precision (serial/exhaustive.c is FP64 throughout), so
 //     this is the kernel the parity tests hold to 1e-10 / 1e-12;
 //   * bodies are double4 {x,y,z,m} (32 B), two i-bodies per thread;
-//   * pow(r2, -1.5) (serial/exhaustive.c:173) becomes y^3 with y = r2^-1/2 from
-//     MUFU.RSQ64H (rsqrt.approx.ftz.f64, ~2^-22) refined by one cubically
-//     convergent step: e = 1 - r2*y0^2 ; y = y0 + y0*e*(1/2 + 3/8 e)
-//     (relative error ~ (5/16) e^3 < 2^-60), 5 DFMA-pipe operations;
+//   * pow(r2, -1.5) (serial/exhaustive.c:173) starts from y0 = r2^-1/2 of
+//     MUFU.RSQ64H (rsqrt.approx.ftz.f64, relative error e ~ 2^-20) and corrects
+//     the CUBE directly: with e = 1 - r2*y0^2,
+//         r2^-3/2 = y0^3 (1 - e)^-3/2 = y0^3 (1 + e (3/2 + 15/8 e) + O(e^3)),
+//     O(e^3) < 2^-58.  y0^2 is shared by e and the cube: 7 FP64 operations for
+//     m * r2^-3/2;
 //   * accumulation is plain FP64 in j order inside a CTA's j-range; partial
 //     ranges are added in fixed slot order.
-// Per interaction: 3 DADD + 6 DFMA + 5 (rsqrt) + 3 DMUL = 17 FP64-pipe
-// operations + 1 MUFU.
+// Per interaction: 3 DADD + 3 DFMA (r2) + 7 + 3 DFMA = 16 FP64-pipe operations
+// + 1 MUFU.
 #include "nb_direct.cuh"
 
 namespace nb {
@@ -30,14 +32,13 @@ __device__ __forceinline__ void named_sync64(int id, int nthreads)
 __device__ __forceinline__ double inv_r3_times_m(double r2, double m)
 {
     const double y0 = rsqrt_approx_f64(r2);
-    const double t = r2 * y0;
-    const double e = fma(-t, y0, 1.0);
-    const double pe = fma(0.375, e, 0.5);
-    const double ye = y0 * e;
-    const double y = fma(ye, pe, y0);
-    const double y2 = y * y;
-    const double my = m * y;
-    return y2 * my;
+    const double y02 = y0 * y0;
+    const double e = fma(-r2, y02, 1.0);
+    const double pe = fma(1.875, e, 1.5);
+    const double q = e * pe;
+    const double my = m * y0;
+    const double u = y02 * my;
+    return fma(u, q, u);
 }
 
 // v += (a*dt)/2.0 and x += v*dt with the reference's roundings
@@ -52,7 +53,7 @@ __device__ __forceinline__ double drift64(double x, double v, double dt)
 }
 
 template <int NW, int TB, int MINB>
-__global__ void __launch_bounds__((NW + 1) * 32, MINB)
+__global__ void __launch_bounds__(NW * 32, MINB)
     direct_f64_kernel(const StepParams p)
 {
     constexpr int TPB = NW * 32;  // compute threads
@@ -62,7 +63,6 @@ __global__ void __launch_bounds__((NW + 1) * 32, MINB)
     __shared__ __align__(8) uint64_t empty_bar[STAGES64];
     __shared__ unsigned s_last;
 
-    const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const double4 *__restrict__ q = static_cast<const double4 *>(p.q_cur);
 
@@ -80,23 +80,22 @@ __global__ void __launch_bounds__((NW + 1) * 32, MINB)
     const unsigned long long w1 = p.ws.bound(blockIdx.x + 1);
     const unsigned n_jtiles = p.ws.n_jtiles;
 
-    if (warp == NW) {
-        if (lane == 0) {
-            unsigned stage = 0, phase = 0;
-            unsigned t = (unsigned)(w0 % n_jtiles);
-            for (unsigned long long w = w0; w < w1; ++w) {
-                mbar_wait(&empty_bar[stage], phase ^ 1u);
-                const unsigned first = t * TB;
-                const unsigned nb = min((unsigned)TB, p.n_units - first);
-                const unsigned bytes = nb * 32u;
-                mbar_arrive_expect_tx(&full_bar[stage], bytes);
-                tma_load_1d(&tiles[stage][0], q + first, bytes, &full_bar[stage]);
-                if (++stage == STAGES64) { stage = 0; phase ^= 1u; }
-                if (++t == n_jtiles) t = 0;
-            }
-        }
-        return;
-    }
+    // j-tile ring fed by thread 0, two tiles ahead (see nb_direct_f32.cu)
+    constexpr unsigned AHEAD = STAGES64 - 2;
+    const unsigned n_tiles = (unsigned)(w1 - w0);
+    const unsigned tile0 = (unsigned)(w0 % n_jtiles);
+    auto issue_tile = [&](unsigned k) {
+        const unsigned s = k % STAGES64;
+        if (k >= STAGES64) mbar_wait(&empty_bar[s], ((k / STAGES64) - 1u) & 1u);
+        const unsigned first = ((tile0 + k) % n_jtiles) * TB;
+        const unsigned nb = min((unsigned)TB, p.n_units - first);
+        const unsigned bytes = nb * 32u;
+        mbar_arrive_expect_tx(&full_bar[s], bytes);
+        tma_load_1d(&tiles[s][0], q + first, bytes, &full_bar[s]);
+    };
+    if (threadIdx.x == 0)
+        for (unsigned k = 0; k < AHEAD && k < n_tiles; ++k) issue_tile(k);
+    unsigned kt = 0;
 
     const int tidc = threadIdx.x;
     unsigned stage = 0, phase = 0;
@@ -120,6 +119,8 @@ __global__ void __launch_bounds__((NW + 1) * 32, MINB)
         for (unsigned k = 0; k < cnt; ++k) {
             const unsigned first = (t0 + k) * TB;
             const int nb = (int)min((unsigned)TB, p.n_units - first);
+            if (threadIdx.x == 0 && kt + AHEAD < n_tiles) issue_tile(kt + AHEAD);
+            ++kt;
             mbar_wait(&full_bar[stage], phase);
             const double4 *__restrict__ tile = &tiles[stage][0];
 #pragma unroll 4
@@ -222,8 +223,8 @@ struct VariantF64 {
 };
 constexpr int kNumVariants64 = 3;
 constexpr VariantF64 kVariants64[kNumVariants64] = {
-    {7, 128, 2}, // large : i-block 448 bodies
-    {3, 128, 4}, // medium: i-block 192 bodies
+    {8, 128, 2}, // large : i-block 512 bodies
+    {4, 128, 4}, // medium: i-block 256 bodies
     {1, 32, 8},  // small : i-block 64 bodies
 };
 
@@ -232,7 +233,7 @@ int occupancy64()
 {
     int n = 0;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, direct_f64_kernel<NW, TB, MINB>,
-                                                  (NW + 1) * 32, 0);
+                                                  NW * 32, 0);
     return n;
 }
 } // namespace
@@ -252,12 +253,12 @@ cudaError_t plan_direct_f64(DirectPlan *plan, unsigned slice_units, unsigned n_u
     plan->units_per_tile = (unsigned)k.tb;
     plan->n_iblocks = (slice_units + plan->units_per_iblock - 1) / plan->units_per_iblock;
     plan->n_jtiles = (n_units + plan->units_per_tile - 1) / plan->units_per_tile;
-    plan->block = (unsigned)(k.nw + 1) * 32u;
+    plan->block = (unsigned)k.nw * 32u;
     plan->slot_doubles = (size_t)k.nw * 32 * 6;
     int occ = 0;
     switch (v) {
-    case 0: occ = occupancy64<7, 128, 2>(); break;
-    case 1: occ = occupancy64<3, 128, 4>(); break;
+    case 0: occ = occupancy64<8, 128, 2>(); break;
+    case 1: occ = occupancy64<4, 128, 4>(); break;
     default: occ = occupancy64<1, 32, 8>(); break;
     }
     cudaError_t err = cudaGetLastError();
@@ -278,8 +279,8 @@ cudaError_t launch_direct_f64(const DirectPlan &plan, StepParams p, int tune_fla
     p.ws = WorkSplit{(unsigned long long)plan.n_iblocks * plan.n_jtiles, plan.n_iblocks,
                      plan.n_jtiles, plan.grid};
     switch (plan.variant) {
-    case 0: direct_f64_kernel<7, 128, 2><<<plan.grid, plan.block, 0, stream>>>(p); break;
-    case 1: direct_f64_kernel<3, 128, 4><<<plan.grid, plan.block, 0, stream>>>(p); break;
+    case 0: direct_f64_kernel<8, 128, 2><<<plan.grid, plan.block, 0, stream>>>(p); break;
+    case 1: direct_f64_kernel<4, 128, 4><<<plan.grid, plan.block, 0, stream>>>(p); break;
     default: direct_f64_kernel<1, 32, 8><<<plan.grid, plan.block, 0, stream>>>(p); break;
     }
     return cudaGetLastError();
