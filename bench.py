@@ -249,6 +249,17 @@ def run_gpu_arm(args):
     total_interactions = float(args.steps) * float(n) * float(n)
     value = total_interactions / (dev_ms * 1e-3)
 
+    # ---- the same K steps enqueued back to back (one nb_step call, no L2 flush, no host sync
+    # in between): what a simulation run sees; with world > 1 the all-gather of step k overlaps
+    # the own-slice launch of step k+1 here.  Reported beside `value`, not instead of it.
+    barrier()
+    eng.step(args.steps)
+    stb = eng.stats()
+    tb = torch.tensor([stb.last_step_ms], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(tb, op=dist.ReduceOp.MAX)
+    b2b_ms = float(tb[0]) / args.steps
+
     # ---- end to end through the C ABI with host buffers -----------------------------------
     # one e2e step = propagation() of one time step from host arrays: H2D of positions and
     # velocities (pinned), kick+drift launch, closing force launch, D2H of the new state;
@@ -306,6 +317,9 @@ def run_gpu_arm(args):
                     "what": "nb_upload + nb_step(1) + nb_gather(pos, vel) per step, pinned host buffers",
                     "checksum": checksum},
             "gpu_launches": int(launches),
+            "back_to_back": {"ms_per_step": b2b_ms, "value": float(n) * float(n) / (b2b_ms * 1e-3),
+                             "split_evaluations": int(stb.split_evaluations),
+                             "collectives": int(stb.collectives)},
             "roofline": roof,
             "grid": st0.grid, "block": st0.block,
         }

@@ -67,6 +67,7 @@ typedef struct nb_config {
 
 #define NB_TUNE_SCALAR_FP32 1 /* FP32 kernel without packed f32x2 instructions */
 #define NB_TUNE_NO_SPLIT 2    /* one CTA per i-block over all j (no j-range splitting) */
+#define NB_TUNE_NO_OVERLAP 4  /* world > 1: wait for the all-gather before any force work */
 
 typedef struct nb_stats {
     double last_step_ms;        /* device time (CUDA events on the engine stream) of the last nb_step */
@@ -77,6 +78,8 @@ typedef struct nb_stats {
     unsigned long long steps_done;     /* completed drifts */
     int grid, block, smem_bytes;       /* geometry of the last force launch */
     size_t n, n_padded, slice_begin, slice_end;
+    unsigned long long collectives;       /* all-gathers issued since nb_init (world > 1) */
+    unsigned long long split_evaluations; /* force evaluations issued as own-slice + gathered launches */
 } nb_stats;
 
 /* Fills cfg with the reference's constants: FP64, direct, eps2 = 0.01, G = 1,

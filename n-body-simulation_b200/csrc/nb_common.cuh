@@ -97,6 +97,10 @@ enum : unsigned {
     NB_F_KICK2 = 1u,      // finish the previous step: v += a*dt/2
     NB_F_KICK1_DRIFT = 2u, // start the next step:     v += a*dt/2 ; x' = x + v*dt
     NB_F_STORE_ACC = 4u,  // keep a(x) for a later cheap kick+drift / for nb_accelerations
+    // multi-rank overlap: the force sum is cut into "own slice j-tiles" (needs no
+    // communication) and "everybody else's j-tiles" (after the all-gather landed)
+    NB_F_PARTIAL_OUT = 8u, // park the raw FP64 sums in `partial`, no epilogue
+    NB_F_PARTIAL_IN = 16u, // start from the sums parked in `partial`
 };
 
 struct StepParams {
@@ -105,12 +109,15 @@ struct StepParams {
     void *vel;         // velocities, all bodies (own slice touched)
     void *acc;         // stored accelerations (own slice), or nullptr
     double *workspace; // partial-sum slots
+    double *partial;    // parked sums of a PARTIAL_OUT launch (own slice), or nullptr
     unsigned *counters; // one per i-block, zero between launches
     unsigned n_real;    // real bodies (global)
     unsigned n_units;   // j extent in layout units (quads for FP32, bodies for FP64), padded
     unsigned i_begin;   // first i unit of this rank's slice
     unsigned i_end;     // one past the last i unit of the slice
     unsigned max_slots; // workspace slots per i-block
+    unsigned jt_begin;  // first j-tile of this launch (global tile index); tiles wrap modulo jt_total
+    unsigned jt_total;  // j-tiles covering all n_units; ws.n_jtiles is this launch's share
     unsigned flags;
     double dt, eps2, G;
     WorkSplit ws;

@@ -27,6 +27,10 @@ namespace nb {
 namespace {
 
 constexpr int STAGES = 4;
+#ifndef NB_F32_UNROLL
+#define NB_F32_UNROLL 1 // j-quads per inner-loop trip; 1 measured fastest (63.97 vs 65.63 ms at 400k bodies for 2, 65.76 for 4)
+#endif
+constexpr int kUnrollJ = NB_F32_UNROLL;
 
 __device__ __forceinline__ void named_sync(int id, int nthreads)
 {
@@ -138,10 +142,14 @@ __global__ void __launch_bounds__(NW * 32, MINB)
     constexpr unsigned AHEAD = STAGES - 2;
     const unsigned n_tiles = (unsigned)(w1 - w0);
     const unsigned tile0 = (unsigned)(w0 % n_jtiles);
+    auto global_tile = [&](unsigned t) {
+        const unsigned g = p.jt_begin + t;
+        return g >= p.jt_total ? g - p.jt_total : g;
+    };
     auto issue_tile = [&](unsigned k) {
         const unsigned s = k % STAGES;
         if (k >= STAGES) mbar_wait(&empty_bar[s], ((k / STAGES) - 1u) & 1u);
-        const unsigned first = ((tile0 + k) % n_jtiles) * TQ;
+        const unsigned first = global_tile((tile0 + k) % n_jtiles) * TQ;
         const unsigned nq = min((unsigned)TQ, p.n_units - first);
         const unsigned bytes = nq * 64u;
         mbar_arrive_expect_tx(&full_bar[s], bytes);
@@ -172,7 +180,7 @@ __global__ void __launch_bounds__(NW * 32, MINB)
         for (int c = 0; c < 12; ++c) dacc[c][tidc] = 0.0;
 
         for (unsigned k = 0; k < cnt; ++k) {
-            const unsigned first = (t0 + k) * TQ;
+            const unsigned first = global_tile(t0 + k) * TQ;
             const int nq = (int)min((unsigned)TQ, p.n_units - first);
             float2 ax[4], ay[4], az[4];
 #pragma unroll
@@ -182,7 +190,7 @@ __global__ void __launch_bounds__(NW * 32, MINB)
             ++kt;
             mbar_wait(&full_bar[stage], phase);
             const float4 *__restrict__ tile = &tiles[stage][0];
-#pragma unroll 2
+#pragma unroll kUnrollJ
             for (int jq = 0; jq < nq; ++jq) {
                 const float4 JX = tile[jq * 4 + 0];
                 const float4 JY = tile[jq * 4 + 1];
@@ -264,6 +272,28 @@ __global__ void __launch_bounds__(NW * 32, MINB)
             named_sync(1, QPB); // s_last may be rewritten by the next i-block
         }
 
+        // ---------------- multi-rank: sums parked between the two j-ranges --------
+        if (do_epilogue && (p.flags & (NB_F_PARTIAL_IN | NB_F_PARTIAL_OUT))) {
+            double2 *park = reinterpret_cast<double2 *>(p.partial) + (size_t)ib * (QPB * 6);
+            if (p.flags & NB_F_PARTIAL_IN) {
+                double2 v;
+                v = park[0 * QPB + tidc]; dax[0] += v.x; dax[1] += v.y;
+                v = park[1 * QPB + tidc]; dax[2] += v.x; dax[3] += v.y;
+                v = park[2 * QPB + tidc]; day[0] += v.x; day[1] += v.y;
+                v = park[3 * QPB + tidc]; day[2] += v.x; day[3] += v.y;
+                v = park[4 * QPB + tidc]; daz[0] += v.x; daz[1] += v.y;
+                v = park[5 * QPB + tidc]; daz[2] += v.x; daz[3] += v.y;
+            } else {
+                park[0 * QPB + tidc] = make_double2(dax[0], dax[1]);
+                park[1 * QPB + tidc] = make_double2(dax[2], dax[3]);
+                park[2 * QPB + tidc] = make_double2(day[0], day[1]);
+                park[3 * QPB + tidc] = make_double2(day[2], day[3]);
+                park[4 * QPB + tidc] = make_double2(daz[0], daz[1]);
+                park[5 * QPB + tidc] = make_double2(daz[2], daz[3]);
+                do_epilogue = false;
+            }
+        }
+
         // ---------------- epilogue: kick2 / kick1 / drift, one HBM round trip ------
         if (do_epilogue && valid) {
             float a[3][4];
@@ -311,23 +341,55 @@ __global__ void __launch_bounds__(NW * 32, MINB)
 } // namespace
 
 // ------------------------------------------------------------------ host ----
-void finish_plan(DirectPlan *plan, int tune_flags)
+static void fill_geom(const DirectPlan &plan, LaunchGeom *g, int tune_flags)
 {
-    const unsigned long long total = (unsigned long long)plan->n_iblocks * plan->n_jtiles;
-    if (tune_flags & 2 /* NB_TUNE_NO_SPLIT */) plan->grid = plan->n_iblocks;
-    if ((unsigned long long)plan->grid > total) plan->grid = (unsigned)total;
-    if (plan->grid == 0) plan->grid = 1;
-    WorkSplit ws{total, plan->n_iblocks, plan->n_jtiles, plan->grid};
-    unsigned max_slots = 1;
-    for (unsigned ib = 0; ib < plan->n_iblocks; ++ib) {
-        const unsigned long long x0 = (unsigned long long)ib * plan->n_jtiles;
-        const unsigned s = ws.owner(x0 + plan->n_jtiles - 1) - ws.owner(x0) + 1;
-        if (s > max_slots) max_slots = s;
+    const unsigned long long total = (unsigned long long)plan.n_iblocks * g->n_jtiles;
+    g->grid = (tune_flags & 2 /* NB_TUNE_NO_SPLIT */) ? plan.n_iblocks : plan.grid;
+    if ((unsigned long long)g->grid > total) g->grid = (unsigned)total;
+    if (g->grid == 0) g->grid = 1;
+    WorkSplit ws{total, plan.n_iblocks, g->n_jtiles, g->grid};
+    g->max_slots = 1;
+    for (unsigned ib = 0; ib < plan.n_iblocks && total; ++ib) {
+        const unsigned long long x0 = (unsigned long long)ib * g->n_jtiles;
+        const unsigned s = ws.owner(x0 + g->n_jtiles - 1) - ws.owner(x0) + 1;
+        if (s > g->max_slots) g->max_slots = s;
     }
-    plan->max_slots = max_slots;
+}
+
+void finish_plan(DirectPlan *plan, const SliceGeom &sg, int tune_flags)
+{
+    const unsigned T = plan->units_per_tile;
+    plan->geom[NB_GEOM_FULL] = LaunchGeom{plan->n_jtiles, 0, 0, 1};
+    plan->can_split = sg.own_units < sg.n_units && sg.own_units % T == 0 && sg.own_begin % T == 0;
+    if (plan->can_split) {
+        const unsigned own_tiles = sg.own_units / T, first = sg.own_begin / T;
+        plan->geom[NB_GEOM_OWN] = LaunchGeom{own_tiles, first, 0, 1};
+        plan->geom[NB_GEOM_REST] =
+            LaunchGeom{plan->n_jtiles - own_tiles, (first + own_tiles) % plan->n_jtiles, 0, 1};
+    } else {
+        plan->geom[NB_GEOM_OWN] = plan->geom[NB_GEOM_REST] = plan->geom[NB_GEOM_FULL];
+    }
+    unsigned max_slots = 1;
+    for (int k = 0; k < 3; ++k) {
+        fill_geom(*plan, &plan->geom[k], tune_flags);
+        if (plan->geom[k].max_slots > max_slots) max_slots = plan->geom[k].max_slots;
+    }
+    for (int k = 0; k < 3; ++k) plan->geom[k].max_slots = max_slots; // one workspace stride
     plan->workspace_bytes =
         (size_t)plan->n_iblocks * max_slots * plan->slot_doubles * sizeof(double);
+    plan->partial_bytes =
+        plan->can_split ? (size_t)plan->n_iblocks * plan->slot_doubles * sizeof(double) : 0;
     plan->counter_bytes = (size_t)plan->n_iblocks * sizeof(unsigned);
+}
+
+void apply_geom(const DirectPlan &plan, int geom, StepParams *p)
+{
+    const LaunchGeom &g = plan.geom[geom];
+    p->max_slots = g.max_slots;
+    p->jt_begin = g.jt_begin;
+    p->jt_total = plan.n_jtiles;
+    p->ws = WorkSplit{(unsigned long long)plan.n_iblocks * g.n_jtiles, plan.n_iblocks, g.n_jtiles,
+                      g.grid};
 }
 
 namespace {
@@ -349,9 +411,9 @@ cudaError_t launch_variant(const DirectPlan &plan, const StepParams &p, bool pac
                            cudaStream_t stream)
 {
     if (packed)
-        direct_f32_kernel<NW, TQ, true, MINB><<<plan.grid, plan.block, 0, stream>>>(p);
+        direct_f32_kernel<NW, TQ, true, MINB><<<p.ws.n_ctas, plan.block, 0, stream>>>(p);
     else
-        direct_f32_kernel<NW, TQ, false, MINB><<<plan.grid, plan.block, 0, stream>>>(p);
+        direct_f32_kernel<NW, TQ, false, MINB><<<p.ws.n_ctas, plan.block, 0, stream>>>(p);
     return cudaGetLastError();
 }
 
@@ -369,9 +431,10 @@ int occupancy_variant(bool packed)
 }
 } // namespace
 
-cudaError_t plan_direct_f32(DirectPlan *plan, unsigned slice_units, unsigned n_units, int sm_count,
-                            int ctas_per_sm, int tune_flags)
+cudaError_t plan_direct_f32(DirectPlan *plan, const SliceGeom &sg, int sm_count, int ctas_per_sm,
+                            int tune_flags)
 {
+    const unsigned slice_units = sg.slice_units, n_units = sg.n_units;
     const unsigned slice_bodies = slice_units * 4u;
     int v = 0;
     if (slice_bodies < 16384u) v = 2;
@@ -400,16 +463,14 @@ cudaError_t plan_direct_f32(DirectPlan *plan, unsigned slice_units, unsigned n_u
     int per_sm = ctas_per_sm > 0 ? ctas_per_sm : k.minb;
     if (per_sm > occ) per_sm = occ;
     plan->grid = (unsigned)(sm_count * per_sm);
-    finish_plan(plan, tune_flags);
+    finish_plan(plan, sg, tune_flags);
     return cudaSuccess;
 }
 
-cudaError_t launch_direct_f32(const DirectPlan &plan, StepParams p, int tune_flags,
+cudaError_t launch_direct_f32(const DirectPlan &plan, int geom, StepParams p, int tune_flags,
                               cudaStream_t stream)
 {
-    p.max_slots = plan.max_slots;
-    p.ws = WorkSplit{(unsigned long long)plan.n_iblocks * plan.n_jtiles, plan.n_iblocks,
-                     plan.n_jtiles, plan.grid};
+    apply_geom(plan, geom, &p);
     const bool packed = !(tune_flags & 1);
     switch (plan.variant) {
     case 0: return launch_variant<8, 64, 2>(plan, p, packed, stream);

@@ -84,10 +84,14 @@ __global__ void __launch_bounds__(NW * 32, MINB)
     constexpr unsigned AHEAD = STAGES64 - 2;
     const unsigned n_tiles = (unsigned)(w1 - w0);
     const unsigned tile0 = (unsigned)(w0 % n_jtiles);
+    auto global_tile = [&](unsigned t) {
+        const unsigned g = p.jt_begin + t;
+        return g >= p.jt_total ? g - p.jt_total : g;
+    };
     auto issue_tile = [&](unsigned k) {
         const unsigned s = k % STAGES64;
         if (k >= STAGES64) mbar_wait(&empty_bar[s], ((k / STAGES64) - 1u) & 1u);
-        const unsigned first = ((tile0 + k) % n_jtiles) * TB;
+        const unsigned first = global_tile((tile0 + k) % n_jtiles) * TB;
         const unsigned nb = min((unsigned)TB, p.n_units - first);
         const unsigned bytes = nb * 32u;
         mbar_arrive_expect_tx(&full_bar[s], bytes);
@@ -117,7 +121,7 @@ __global__ void __launch_bounds__(NW * 32, MINB)
         double ax[2] = {0, 0}, ay[2] = {0, 0}, az[2] = {0, 0};
 
         for (unsigned k = 0; k < cnt; ++k) {
-            const unsigned first = (t0 + k) * TB;
+            const unsigned first = global_tile(t0 + k) * TB;
             const int nb = (int)min((unsigned)TB, p.n_units - first);
             if (threadIdx.x == 0 && kt + AHEAD < n_tiles) issue_tile(kt + AHEAD);
             ++kt;
@@ -183,6 +187,22 @@ __global__ void __launch_bounds__(NW * 32, MINB)
             named_sync64(1, TPB);
         }
 
+        // multi-rank: sums parked between the own-slice and the gathered j-ranges
+        if (do_epilogue && (p.flags & (NB_F_PARTIAL_IN | NB_F_PARTIAL_OUT))) {
+            double2 *park = reinterpret_cast<double2 *>(p.partial) + (size_t)ib * (TPB * 3);
+            if (p.flags & NB_F_PARTIAL_IN) {
+                double2 v;
+                v = park[0 * TPB + tidc]; ax[0] += v.x; ax[1] += v.y;
+                v = park[1 * TPB + tidc]; ay[0] += v.x; ay[1] += v.y;
+                v = park[2 * TPB + tidc]; az[0] += v.x; az[1] += v.y;
+            } else {
+                park[0 * TPB + tidc] = make_double2(ax[0], ax[1]);
+                park[1 * TPB + tidc] = make_double2(ay[0], ay[1]);
+                park[2 * TPB + tidc] = make_double2(az[0], az[1]);
+                do_epilogue = false;
+            }
+        }
+
         if (do_epilogue) {
 #pragma unroll
             for (int r = 0; r < 2; ++r) {
@@ -238,9 +258,10 @@ int occupancy64()
 }
 } // namespace
 
-cudaError_t plan_direct_f64(DirectPlan *plan, unsigned slice_units, unsigned n_units, int sm_count,
-                            int ctas_per_sm, int tune_flags)
+cudaError_t plan_direct_f64(DirectPlan *plan, const SliceGeom &sg, int sm_count, int ctas_per_sm,
+                            int tune_flags)
 {
+    const unsigned slice_units = sg.slice_units, n_units = sg.n_units;
     int v = 0;
     if (slice_units < 8192u) v = 2;
     else if (slice_units < 148u * 896u) v = 1;
@@ -267,21 +288,19 @@ cudaError_t plan_direct_f64(DirectPlan *plan, unsigned slice_units, unsigned n_u
     int per_sm = ctas_per_sm > 0 ? ctas_per_sm : k.minb;
     if (per_sm > occ) per_sm = occ;
     plan->grid = (unsigned)(sm_count * per_sm);
-    finish_plan(plan, tune_flags);
+    finish_plan(plan, sg, tune_flags);
     return cudaSuccess;
 }
 
-cudaError_t launch_direct_f64(const DirectPlan &plan, StepParams p, int tune_flags,
+cudaError_t launch_direct_f64(const DirectPlan &plan, int geom, StepParams p, int tune_flags,
                               cudaStream_t stream)
 {
     (void)tune_flags;
-    p.max_slots = plan.max_slots;
-    p.ws = WorkSplit{(unsigned long long)plan.n_iblocks * plan.n_jtiles, plan.n_iblocks,
-                     plan.n_jtiles, plan.grid};
+    apply_geom(plan, geom, &p);
     switch (plan.variant) {
-    case 0: direct_f64_kernel<8, 128, 2><<<plan.grid, plan.block, 0, stream>>>(p); break;
-    case 1: direct_f64_kernel<4, 128, 4><<<plan.grid, plan.block, 0, stream>>>(p); break;
-    default: direct_f64_kernel<1, 32, 8><<<plan.grid, plan.block, 0, stream>>>(p); break;
+    case 0: direct_f64_kernel<8, 128, 2><<<p.ws.n_ctas, plan.block, 0, stream>>>(p); break;
+    case 1: direct_f64_kernel<4, 128, 4><<<p.ws.n_ctas, plan.block, 0, stream>>>(p); break;
+    default: direct_f64_kernel<1, 32, 8><<<p.ws.n_ctas, plan.block, 0, stream>>>(p); break;
     }
     return cudaGetLastError();
 }

@@ -7,7 +7,14 @@
 // launch at x_k carries kick2 of step k-1 and kick1+drift of step k:
 //   SYNCED_NOACC --[F,K1,D]--> MIDSTEP --[F,K2,K1,D]--> MIDSTEP ... --[F,K2,store a]--> SYNCED_ACC
 //   SYNCED_ACC   --[K1,D from stored a]--> MIDSTEP
-// n steps + a gather with velocities = n+1 force launches, the reference's count.
+// n steps + a gather with velocities = n+1 force evaluations, the reference's count.
+//
+// Multi-rank (world > 1): every rank owns an i-slice and holds all positions.
+// After a drift the own slices are re-assembled by ncclAllGather on a side
+// stream; the next force evaluation is issued as two launches on the compute
+// stream -- first the j-tiles of the rank's own slice (already valid), then,
+// behind an event wait on the all-gather, everybody else's j-tiles + epilogue
+// -- so the exchange over NVLink is hidden behind compute.
 #include <dlfcn.h>
 #include <new>
 #include <stdio.h>
@@ -103,13 +110,17 @@ struct nb_engine {
     unsigned slice_units = 0; // units per rank
     unsigned i_begin = 0, i_end = 0;
     int sm_count = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;      // compute
+    cudaStream_t comm_stream = nullptr; // NCCL collectives (world > 1)
+    cudaEvent_t ev_compute = nullptr, ev_gather = nullptr; // hand-offs between the two
+    bool gather_pending = false; // an all-gather is in flight on comm_stream
+    bool step_ended_in_gather = false;
     cudaEvent_t ev_step0 = nullptr, ev_step1 = nullptr, ev_f0 = nullptr, ev_f1 = nullptr;
     bool have_step_ev = false, have_force_ev = false;
     void *q[2] = {nullptr, nullptr};
     int cur = 0;
     void *vel = nullptr, *acc = nullptr;
-    double *workspace = nullptr;
+    double *workspace = nullptr, *partial = nullptr;
     unsigned *counters = nullptr;
     double *stage_pos = nullptr, *stage_vel = nullptr; // host-packing staging, n*4 / n*3 doubles
     double *energy_part = nullptr;
@@ -128,12 +139,40 @@ int set_device(nb_engine *e)
     return NB_OK;
 }
 
+// The compute stream may not touch gathered data before the collective landed.
+int wait_gather(nb_engine *e)
+{
+    if (!e->gather_pending) return NB_OK;
+    NB_CUDA(cudaStreamWaitEvent(e->stream, e->ev_gather, 0));
+    e->gather_pending = false;
+    return NB_OK;
+}
+
+// In-place all-gather of every rank's slice of `buf`, on the side stream, after
+// everything enqueued on the compute stream so far.  Returns without waiting:
+// consumers call wait_gather().
 int all_gather_units(nb_engine *e, void *buf, size_t unit_bytes)
 {
     if (e->cfg.world <= 1) return NB_OK;
     const size_t bytes = (size_t)e->slice_units * unit_bytes;
     const char *send = (const char *)buf + (size_t)e->cfg.rank * bytes;
-    NB_NCCL(g_nccl.AllGather(send, buf, bytes, /*ncclInt8*/ 0, e->comm, e->stream));
+    NB_CUDA(cudaEventRecord(e->ev_compute, e->stream));
+    NB_CUDA(cudaStreamWaitEvent(e->comm_stream, e->ev_compute, 0));
+    NB_NCCL(g_nccl.AllGather(send, buf, bytes, /*ncclInt8*/ 0, e->comm, e->comm_stream));
+    NB_CUDA(cudaEventRecord(e->ev_gather, e->comm_stream));
+    e->gather_pending = true;
+    e->step_ended_in_gather = false; // nb_step sets it again for the gather that ends a step
+    e->st.collectives++;
+    return NB_OK;
+}
+
+int launch_kernel(nb_engine *e, int geom, const StepParams &p)
+{
+    if (e->cfg.precision == NB_PREC_FP32)
+        NB_CUDA(launch_direct_f32(e->plan, geom, p, e->cfg.tune_flags, e->stream));
+    else
+        NB_CUDA(launch_direct_f64(e->plan, geom, p, e->cfg.tune_flags, e->stream));
+    e->st.kernel_launches++;
     return NB_OK;
 }
 
@@ -149,6 +188,7 @@ int launch_force(nb_engine *e, unsigned flags)
     p.vel = e->vel;
     p.acc = e->acc;
     p.workspace = e->workspace;
+    p.partial = e->partial;
     p.counters = e->counters;
     p.n_real = (unsigned)e->n;
     p.n_units = e->n_units;
@@ -159,14 +199,23 @@ int launch_force(nb_engine *e, unsigned flags)
     p.eps2 = e->cfg.eps2;
     p.G = e->cfg.G;
     NB_CUDA(cudaEventRecord(e->ev_f0, e->stream));
-    if (e->cfg.precision == NB_PREC_FP32)
-        NB_CUDA(launch_direct_f32(e->plan, p, e->cfg.tune_flags, e->stream));
-    else
-        NB_CUDA(launch_direct_f64(e->plan, p, e->cfg.tune_flags, e->stream));
+    int rc;
+    if (e->gather_pending && e->plan.can_split && !(e->cfg.tune_flags & NB_TUNE_NO_OVERLAP)) {
+        // positions of the other ranks are still in flight: start on the own slice
+        StepParams a = p;
+        a.flags = NB_F_PARTIAL_OUT;
+        if ((rc = launch_kernel(e, NB_GEOM_OWN, a))) return rc;
+        if ((rc = wait_gather(e))) return rc;
+        p.flags |= NB_F_PARTIAL_IN;
+        if ((rc = launch_kernel(e, NB_GEOM_REST, p))) return rc;
+        e->st.split_evaluations++;
+    } else {
+        if ((rc = wait_gather(e))) return rc;
+        if ((rc = launch_kernel(e, NB_GEOM_FULL, p))) return rc;
+    }
     NB_CUDA(cudaEventRecord(e->ev_f1, e->stream));
     e->have_force_ev = true;
     e->st.force_launches++;
-    e->st.kernel_launches++;
     e->st.interactions += (unsigned long long)(e->i_end - e->i_begin) * e->unit_bodies *
                           (unsigned long long)e->n_units * e->unit_bodies;
     if (flags & (NB_F_KICK2 | NB_F_KICK1_DRIFT)) e->vel_complete = (e->cfg.world <= 1);
@@ -193,12 +242,14 @@ int ensure_vel_complete(nb_engine *e)
     int rc = all_gather_units(e, e->vel, e->vel_unit_bytes);
     if (rc) return rc;
     e->vel_complete = true;
-    return NB_OK;
+    return wait_gather(e);
 }
 
 int upload(nb_engine *e, const double *pos, const double *vel)
 {
     const size_t n = e->n;
+    int wrc = wait_gather(e); // an all-gather may still be writing the position buffers
+    if (wrc) return wrc;
     if (n) {
         NB_CUDA(cudaMemcpyAsync(e->stage_pos, pos, n * 4 * sizeof(double), cudaMemcpyHostToDevice,
                                 e->stream));
@@ -278,15 +329,17 @@ void nb_free(nb_engine *e)
 {
     if (!e) return;
     cudaSetDevice(e->cfg.device);
+    if (e->comm_stream) cudaStreamSynchronize(e->comm_stream);
     if (e->stream) cudaStreamSynchronize(e->stream);
     if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
-    void *bufs[] = {e->q[0], e->q[1], e->vel, e->acc, e->workspace, e->counters,
+    void *bufs[] = {e->q[0], e->q[1], e->vel, e->acc, e->workspace, e->partial, e->counters,
                     e->stage_pos, e->stage_vel, e->energy_part};
     for (void *b : bufs)
         if (b) cudaFree(b);
-    cudaEvent_t evs[] = {e->ev_step0, e->ev_step1, e->ev_f0, e->ev_f1};
+    cudaEvent_t evs[] = {e->ev_step0, e->ev_step1, e->ev_f0, e->ev_f1, e->ev_compute, e->ev_gather};
     for (cudaEvent_t ev : evs)
         if (ev) cudaEventDestroy(ev);
+    if (e->comm_stream) cudaStreamDestroy(e->comm_stream);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -308,15 +361,22 @@ static int init_impl(nb_engine *e, const double *pos, const double *vel)
     NB_CUDA(cudaEventCreate(&e->ev_step1));
     NB_CUDA(cudaEventCreate(&e->ev_f0));
     NB_CUDA(cudaEventCreate(&e->ev_f1));
+    if (c.world > 1) {
+        NB_CUDA(cudaStreamCreateWithFlags(&e->comm_stream, cudaStreamNonBlocking));
+        NB_CUDA(cudaEventCreateWithFlags(&e->ev_compute, cudaEventDisableTiming));
+        NB_CUDA(cudaEventCreate(&e->ev_gather)); // timed: a step ends when its all-gather landed
+    }
 
     const bool f32 = c.precision == NB_PREC_FP32;
     e->unit_bodies = f32 ? 4u : 1u;
     e->unit_bytes = f32 ? 64 : 32;
     e->vel_unit_bytes = f32 ? 48 : 32;
-    // slices: equal unit counts per rank (in-place all-gather), multiple of 32 units
+    // slices: equal unit counts per rank (in-place all-gather), on j-tile boundaries so the
+    // force sum can be cut into "own slice" and "gathered" tiles
     const size_t units = (e->n + e->unit_bodies - 1) / e->unit_bodies;
     size_t per = (units + c.world - 1) / c.world;
-    if (c.world > 1) per = (per + 31) / 32 * 32;
+    const size_t align = f32 ? kSliceAlignF32 : kSliceAlignF64;
+    if (c.world > 1) per = (per + align - 1) / align * align;
     if (per == 0) per = 1;
     if (per * (size_t)c.world * e->unit_bodies > 0x7fffffffu) {
         set_err("nb_init", "too many bodies for 32-bit indices");
@@ -331,10 +391,9 @@ static int init_impl(nb_engine *e, const double *pos, const double *vel)
     if (e->i_end > real_units) e->i_end = real_units > e->i_begin ? real_units : e->i_begin;
 
     const unsigned my_units = e->i_end - e->i_begin;
-    cudaError_t pe = f32 ? plan_direct_f32(&e->plan, my_units ? my_units : 1, e->n_units,
-                                           e->sm_count, c.tune_ctas_per_sm, c.tune_flags)
-                         : plan_direct_f64(&e->plan, my_units ? my_units : 1, e->n_units,
-                                           e->sm_count, c.tune_ctas_per_sm, c.tune_flags);
+    const SliceGeom sg{my_units ? my_units : 1, e->n_units, (unsigned)(per * c.rank), (unsigned)per};
+    cudaError_t pe = f32 ? plan_direct_f32(&e->plan, sg, e->sm_count, c.tune_ctas_per_sm, c.tune_flags)
+                         : plan_direct_f64(&e->plan, sg, e->sm_count, c.tune_ctas_per_sm, c.tune_flags);
     NB_CUDA(pe);
 
     const size_t qbytes = (size_t)e->n_units * e->unit_bytes;
@@ -345,6 +404,7 @@ static int init_impl(nb_engine *e, const double *pos, const double *vel)
     NB_CUDA(cudaMalloc(&e->acc, vbytes));
     NB_CUDA(cudaMemsetAsync(e->acc, 0, vbytes, e->stream));
     NB_CUDA(cudaMalloc(&e->workspace, e->plan.workspace_bytes ? e->plan.workspace_bytes : 16));
+    if (e->plan.partial_bytes) NB_CUDA(cudaMalloc(&e->partial, e->plan.partial_bytes));
     NB_CUDA(cudaMalloc(&e->counters, e->plan.counter_bytes ? e->plan.counter_bytes : 16));
     NB_CUDA(cudaMemsetAsync(e->counters, 0, e->plan.counter_bytes ? e->plan.counter_bytes : 16,
                             e->stream));
@@ -374,7 +434,7 @@ static int init_impl(nb_engine *e, const double *pos, const double *vel)
     e->st.slice_end = (size_t)e->i_end * e->unit_bodies;
     if (e->st.slice_end > e->n) e->st.slice_end = e->n;
     if (e->st.slice_begin > e->n) e->st.slice_begin = e->n;
-    e->st.grid = (int)e->plan.grid;
+    e->st.grid = (int)e->plan.geom[NB_GEOM_FULL].grid;
     e->st.block = (int)e->plan.block;
     return NB_OK;
 }
@@ -451,6 +511,7 @@ int nb_step(nb_engine *e, int n_steps)
     }
     NB_CUDA(cudaEventRecord(e->ev_step1, e->stream));
     e->have_step_ev = true;
+    e->step_ended_in_gather = e->gather_pending && n_steps > 0;
     return NB_OK;
 }
 
@@ -460,6 +521,7 @@ int nb_sync(nb_engine *e)
     int rc = set_device(e);
     if (rc) return rc;
     NB_CUDA(cudaStreamSynchronize(e->stream));
+    if (e->comm_stream) NB_CUDA(cudaStreamSynchronize(e->comm_stream));
     return NB_OK;
 }
 
@@ -481,6 +543,8 @@ int nb_gather(nb_engine *e, double *pos_xyzm, double *vel_xyz)
                                     cudaMemcpyDeviceToHost, e->stream));
     }
     if (pos_xyzm) {
+        rc = wait_gather(e);
+        if (rc) return rc;
         NB_CUDA(unpack_bodies(e->cfg.precision, e->q[e->cur], n, 4, e->stage_pos, e->stream));
         e->st.kernel_launches++;
         if (n)
@@ -505,6 +569,8 @@ int nb_accelerations(nb_engine *e, double *acc_xyz)
     if (rc) return rc;
     rc = all_gather_units(e, e->acc, e->vel_unit_bytes);
     if (rc) return rc;
+    rc = wait_gather(e);
+    if (rc) return rc;
     const unsigned n = (unsigned)e->n;
     NB_CUDA(unpack_bodies(e->cfg.precision, e->acc, n, 3, e->stage_vel, e->stream));
     e->st.kernel_launches++;
@@ -523,6 +589,8 @@ int nb_energy(nb_engine *e, double *KE, double *PE)
     rc = close_step(e);
     if (rc) return rc;
     rc = ensure_vel_complete(e);
+    if (rc) return rc;
+    rc = wait_gather(e);
     if (rc) return rc;
     const unsigned n = (unsigned)e->n;
     NB_CUDA(unpack_bodies(e->cfg.precision, e->vel, n, 3, e->stage_vel, e->stream));
@@ -553,10 +621,15 @@ int nb_get_stats(nb_engine *e, nb_stats *out)
     int rc = set_device(e);
     if (rc) return rc;
     NB_CUDA(cudaStreamSynchronize(e->stream));
+    if (e->comm_stream) NB_CUDA(cudaStreamSynchronize(e->comm_stream));
     float ms = 0.f;
     if (e->have_step_ev) {
         NB_CUDA(cudaEventElapsedTime(&ms, e->ev_step0, e->ev_step1));
         e->st.last_step_ms = ms;
+        if (e->step_ended_in_gather) { // the step is over when the exchange is
+            NB_CUDA(cudaEventElapsedTime(&ms, e->ev_step0, e->ev_gather));
+            if (ms > e->st.last_step_ms) e->st.last_step_ms = ms;
+        }
     }
     if (e->have_force_ev) {
         NB_CUDA(cudaEventElapsedTime(&ms, e->ev_f0, e->ev_f1));

@@ -13,13 +13,14 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libnbody_b200.so")
+LIB_PATH = os.environ.get("NBODY_B200_LIB") or os.path.join(HERE, "libnbody_b200.so")  # override: A/B builds
 HOST_LIB_PATH = os.path.join(HERE, "libnbhost.so")
 
 PREC_FP64, PREC_FP32 = 0, 1
 ALGO_DIRECT, ALGO_BARNES_HUT = 0, 1
 COMM_ID_BYTES = 128
-TUNE_SCALAR_FP32, TUNE_NO_SPLIT = 1, 2
+TUNE_SCALAR_FP32, TUNE_NO_SPLIT, TUNE_NO_OVERLAP = 1, 2, 4
+SLICE_ALIGN = {PREC_FP32: 64, PREC_FP64: 128}  # units; nb_direct.cuh kSliceAlign*
 
 # every symbol include/nbody_engine.h declares
 ABI_SYMBOLS = ["nb_config_default", "nb_init", "nb_upload", "nb_step", "nb_gather",
@@ -42,7 +43,8 @@ class NbStats(C.Structure):
                 ("interactions", C.c_ulonglong), ("steps_done", C.c_ulonglong),
                 ("grid", C.c_int), ("block", C.c_int), ("smem_bytes", C.c_int),
                 ("n", C.c_size_t), ("n_padded", C.c_size_t), ("slice_begin", C.c_size_t),
-                ("slice_end", C.c_size_t)]
+                ("slice_end", C.c_size_t), ("collectives", C.c_ulonglong),
+                ("split_evaluations", C.c_ulonglong)]
 
 
 class NbodyError(RuntimeError):
@@ -132,13 +134,14 @@ def slice_bounds(n, world, rank, precision):
     """The engine's i-slice ownership rule, mirrored for the host side (bodies).
 
     Units are quads (FP32) or bodies (FP64); every rank owns the same number of
-    units, a multiple of 32 when world > 1, the tail padded with massless
-    bodies.  Returns (begin, end) clipped to n."""
+    units, a multiple of the j-tile size when world > 1 (64 quads / 128 bodies),
+    the tail padded with massless bodies.  Returns (begin, end) clipped to n."""
     unit = 4 if precision == PREC_FP32 else 1
     units = (n + unit - 1) // unit
     per = (units + world - 1) // world
     if world > 1:
-        per = (per + 31) // 32 * 32
+        a = SLICE_ALIGN[precision]
+        per = (per + a - 1) // a * a
     per = max(per, 1)
     b, e = per * rank * unit, per * (rank + 1) * unit
     return min(b, n), min(e, n)
