@@ -8,7 +8,7 @@ CC := gcc
 NVFLAGS := --cudart static -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC
 LIB := $(PKG)/libnbody_b200.so
 BIN := $(PKG)/bin
-CU := $(CSRC)/nb_engine.cu $(CSRC)/nb_direct_f32.cu $(CSRC)/nb_direct_f64.cu $(CSRC)/nb_aux.cu
+CU := $(CSRC)/nb_engine.cu $(CSRC)/nb_direct_f32.cu $(CSRC)/nb_direct_f64.cu $(CSRC)/nb_aux.cu $(CSRC)/nb_bh.cu $(CSRC)/nb_bh_sort.cu
 HDR := $(wildcard $(CSRC)/*.cuh) include/nbody_engine.h
 
 .PHONY: all lib host clean

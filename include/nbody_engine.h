@@ -68,6 +68,7 @@ typedef struct nb_config {
 #define NB_TUNE_SCALAR_FP32 1 /* FP32 kernel without packed f32x2 instructions */
 #define NB_TUNE_NO_SPLIT 2    /* one CTA per i-block over all j (no j-range splitting) */
 #define NB_TUNE_NO_OVERLAP 4  /* world > 1: wait for the all-gather before any force work */
+#define NB_TUNE_COUNT_VISITS 8 /* Barnes-Hut: count interactions / node visits (nb_tree_stats) */
 
 typedef struct nb_stats {
     double last_step_ms;        /* device time (CUDA events on the engine stream) of the last nb_step */
@@ -116,6 +117,21 @@ int nb_accelerations(nb_engine *e, double *acc_xyz);
 /* get_energy() of common/get_energy.c:7-47 on the current state, on the GPU
  * (KE, unsoftened PE over i <= j). */
 int nb_energy(nb_engine *e, double *KE, double *PE);
+
+/* Barnes-Hut engines: facts about the octree of the last force evaluation --
+ * what create_tree/add_ents/center_of_mass left behind (serial/barnes-hut.c:
+ * 272-354).  nodes = internal cells (root included), depth counts the root as 1,
+ * root_border = get_bounding_box's max (:326-338).  interactions / node_visits
+ * are totals over this rank's bodies when NB_TUNE_COUNT_VISITS is set.  Returns
+ * NB_E_NOMEM if the node pool or the traversal stack overflowed (the reference
+ * exits in that case, openmp/barnes-hut.c:158-161). */
+typedef struct nb_tree_info {
+    unsigned nodes, depth;
+    double root_border;
+    unsigned long long interactions, node_visits;
+    int pool_overflow, stack_overflow;
+} nb_tree_info;
+int nb_tree_stats(nb_engine *e, nb_tree_info *out);
 
 int nb_sync(nb_engine *e);
 int nb_get_stats(nb_engine *e, nb_stats *out);

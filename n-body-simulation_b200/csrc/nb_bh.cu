@@ -1,0 +1,528 @@
+// nb_bh.cu -- Barnes-Hut on sm_100a: bounding cube, Morton keys, level-wise
+// octree build from the sorted keys, bottom-up centre of mass, warp-cooperative
+// THETA traversal with the leapfrog epilogue fused in.  See nb_bh.cuh for the
+// correspondence with the reference (serial/barnes-hut.c, cuda/barnes-hut.cu).
+#include "nb_bh.cuh"
+#include "nb_common.cuh"
+
+namespace nb {
+namespace {
+
+constexpr int BH_THREADS = 256;
+
+// ---------------------------------------------------------------- bbox ----
+// get_bounding_box (serial/barnes-hut.c:326-338; cuda/barnes-hut.cu:307-349):
+// max over bodies of max(|x|,|y|,|z|); the cube side is twice that.  |v| >= 0,
+// so the IEEE bit pattern orders like the value and atomicMax works on it.
+__global__ void __launch_bounds__(BH_THREADS)
+    bbox_kernel(const double4 *__restrict__ q, unsigned n, unsigned long long *out)
+{
+    double m = 0.0;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const double4 b = q[i];
+        m = fmax(m, fmax(fabs(b.x), fmax(fabs(b.y), fabs(b.z))));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0 && m > 0.0)
+        atomicMax(out, (unsigned long long)__double_as_longlong(m));
+}
+
+// ---------------------------------------------------------------- keys ----
+// The octant path of get_indx_loc (serial/barnes-hut.c:114-133), followed
+// BH_MAX_LEVEL levels down with the reference's own arithmetic (centre +=
+// +-border/4, border /= 2, `>=` goes high), so a body lands in the same cell
+// as in the reference even where the rounded centre decides.  Digit of level 1
+// in the top bits: sorting the keys sorts the bodies depth-first.
+__global__ void __launch_bounds__(BH_THREADS)
+    morton_kernel(const double4 *__restrict__ q, unsigned n, const double *__restrict__ bbox,
+                  uint64_t *__restrict__ key, unsigned *__restrict__ val)
+{
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double4 b = q[i];
+    double border = 2.0 * bbox[0];
+    double cx = 0.0, cy = 0.0, cz = 0.0;
+    uint64_t k = 0;
+#pragma unroll 1
+    for (int l = 0; l < BH_MAX_LEVEL; ++l) {
+        const double q4 = border / 4;
+        const int z = b.z >= cz, y = b.y >= cy, x = b.x >= cx;
+        k = (k << 3) | (uint64_t)(z * 4 + y * 2 + x);
+        cx += x ? q4 : -q4;
+        cy += y ? q4 : -q4;
+        cz += z ? q4 : -q4;
+        border /= 2;
+    }
+    key[i] = k;
+    val[i] = i;
+}
+
+// positions in Morton order + the list of sorted indices this rank integrates
+__global__ void __launch_bounds__(BH_THREADS)
+    gather_sorted_kernel(const double4 *__restrict__ q, const unsigned *__restrict__ perm,
+                         unsigned n, double4 *__restrict__ spos)
+{
+    const unsigned k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n) spos[k] = q[perm[k]];
+}
+
+// Order-preserving compaction of the sorted indices whose body lies in
+// [own_begin, own_end): one CTA pass with a running base (n / 256 iterations of
+// a 256-wide ballot scan; O(n) work, used only when the slice is not everything).
+__global__ void __launch_bounds__(1024)
+    own_list_kernel(const unsigned *__restrict__ perm, unsigned n, unsigned own_begin,
+                    unsigned own_end, unsigned *__restrict__ own, unsigned *__restrict__ n_own)
+{
+    __shared__ unsigned wsum[32];
+    __shared__ unsigned base;
+    if (threadIdx.x == 0) base = 0;
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (unsigned k0 = 0; k0 < n; k0 += 1024) {
+        const unsigned k = k0 + threadIdx.x;
+        const bool mine = k < n && perm[k] >= own_begin && perm[k] < own_end;
+        const unsigned bal = __ballot_sync(0xffffffffu, mine);
+        if (lane == 0) wsum[warp] = __popc(bal);
+        __syncthreads();
+        unsigned before = 0;
+        for (int w = 0; w < warp; ++w) before += wsum[w];
+        if (mine) own[base + before + __popc(bal & ((1u << lane) - 1u))] = k;
+        __syncthreads();
+        if (threadIdx.x == 1023) base += before + __popc(bal);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *n_own = base;
+}
+
+// --------------------------------------------------------------- build ----
+// Nodes are numbered level by level: level L occupies [base_L, base_L + cnt_L),
+// base_L = sum of the counts above.  The kernel of level L splits every node of
+// that level by the key digit of the level into <= 8 children -- a child with
+// one body is a leaf (the body), with >= 2 bodies a new node of level L+1 (the
+// reference's "branch iff the cell holds >= 2 bodies", serial/barnes-hut.c:
+// 190-246).  Eight lanes work on one node, one octant each.
+struct BuildArgs {
+    const uint64_t *key;
+    unsigned *first, *count;
+    unsigned char *level;
+    int *child;
+    unsigned *level_count;
+    unsigned *flags;
+    unsigned node_cap;
+};
+
+__device__ __forceinline__ unsigned level_base(const unsigned *level_count, int L)
+{
+    unsigned b = 0;
+    for (int l = 0; l < L; ++l) b += level_count[l];
+    return b;
+}
+// nodes of level L that exist in the pool (an overflowing level is cut, and flagged)
+__device__ __forceinline__ unsigned level_nodes(const unsigned *level_count, int L, unsigned base,
+                                                unsigned cap)
+{
+    const unsigned c = level_count[L];
+    return base >= cap ? 0u : min(c, cap - base);
+}
+
+__global__ void __launch_bounds__(BH_THREADS) build_level_kernel(BuildArgs a, int L)
+{
+    const unsigned base = level_base(a.level_count, L);
+    const unsigned cnt = level_nodes(a.level_count, L, base, a.node_cap);
+    const unsigned next_base = base + a.level_count[L];
+    const int oct = threadIdx.x & 7;
+    const unsigned gmask = 0xffu << ((threadIdx.x & 31) & ~7); // this node's 8 lanes
+    const int shift = 3 * (BH_MAX_LEVEL - 1 - L);
+    const unsigned groups = (gridDim.x * blockDim.x) >> 3;
+    // all 8 lanes of a group run the same trip count
+    for (unsigned g = (blockIdx.x * blockDim.x + threadIdx.x) >> 3; g < cnt; g += groups) {
+        const unsigned nd = base + g;
+        const unsigned f = a.first[nd], c = a.count[nd];
+        // lower bound of digit `oct` inside [f, f + c)
+        unsigned lo = f, hi = f + c;
+        while (lo < hi) {
+            const unsigned mid = (lo + hi) >> 1;
+            if ((unsigned)((a.key[mid] >> shift) & 7u) < (unsigned)oct) lo = mid + 1;
+            else hi = mid;
+        }
+        const unsigned start = lo;
+        unsigned end = __shfl_down_sync(gmask, start, 1, 8);
+        if (oct == 7) end = f + c;
+        const unsigned k = end - start;
+        const bool branch = k >= 2;
+        const unsigned bal = (__ballot_sync(gmask, branch) >> ((threadIdx.x & 31) & ~7)) & 0xffu;
+        unsigned slot = 0;
+        if (oct == 0 && bal) slot = atomicAdd(&a.level_count[L + 1], (unsigned)__popc(bal));
+        slot = __shfl_sync(gmask, slot, 0, 8);
+        int ch = -1;
+        if (k == 1) ch = (int)start;
+        else if (branch) {
+            const unsigned id = next_base + slot + __popc(bal & ((1u << oct) - 1u));
+            if (id < a.node_cap) {
+                a.first[id] = start;
+                a.count[id] = k;
+                a.level[id] = (unsigned char)(L + 1);
+                ch = -(int)id - 2;
+            } else {
+                a.flags[0] = 1; // node pool exhausted (the reference exits: openmp/barnes-hut.c:158-161)
+            }
+        }
+        a.child[(size_t)nd * 8 + oct] = ch;
+    }
+}
+
+// ----------------------------------------------------------------- COM ----
+// center_of_mass (serial/barnes-hut.c:285-317): children folded in octant
+// order with the reference's incremental weighted mean, written as it writes it
+// (x*m/nm + c*cm/nm), one thread per node, deepest level first.  A level-21
+// node whose bodies share one key ("bucket") folds its bodies in sorted order.
+__global__ void __launch_bounds__(BH_THREADS)
+    com_level_kernel(const double4 *__restrict__ spos, const int *__restrict__ child,
+                     const unsigned *__restrict__ first, const unsigned *__restrict__ count,
+                     const unsigned *__restrict__ level_count, double4 *__restrict__ com, int L,
+                     unsigned node_cap)
+{
+    const unsigned base = level_base(level_count, L);
+    const unsigned cnt = level_nodes(level_count, L, base, node_cap);
+    for (unsigned g = blockIdx.x * blockDim.x + threadIdx.x; g < cnt; g += gridDim.x * blockDim.x) {
+        const unsigned nd = base + g;
+        double cx = 0, cy = 0, cz = 0, cm = 0;
+        auto fold = [&](const double4 &b) {
+            const double nm = __dadd_rn(cm, b.w);
+            cx = __dadd_rn(__ddiv_rn(__dmul_rn(b.x, b.w), nm), __ddiv_rn(__dmul_rn(cx, cm), nm));
+            cy = __dadd_rn(__ddiv_rn(__dmul_rn(b.y, b.w), nm), __ddiv_rn(__dmul_rn(cy, cm), nm));
+            cz = __dadd_rn(__ddiv_rn(__dmul_rn(b.z, b.w), nm), __ddiv_rn(__dmul_rn(cz, cm), nm));
+            cm = nm;
+        };
+        if (L == BH_MAX_LEVEL) {
+            const unsigned f = first[nd], c = count[nd];
+            for (unsigned k = 0; k < c; ++k) fold(spos[f + k]);
+        } else {
+#pragma unroll 1
+            for (int o = 0; o < 8; ++o) {
+                const int ch = child[(size_t)nd * 8 + o];
+                if (ch == -1) continue;
+                fold(ch >= 0 ? spos[ch] : com[-ch - 2]);
+            }
+        }
+        com[nd] = make_double4(cx, cy, cz, cm);
+    }
+}
+
+// ----------------------------------------------------------- traversal ----
+// get_acceleration_rec (serial/barnes-hut.c:389-416) for 32 bodies at a time
+// (consecutive in Morton order), like acceleration_w_stack of the reference
+// (cuda/barnes-hut.cu:538-629): one depth-first walk per warp over a stack in
+// shared memory.  Unlike the reference kernel -- which opens a node for the
+// whole warp unless ALL lanes accept it -- every stack entry carries the mask of
+// lanes still descending: a lane that accepted a cell (border/dist < THETA)
+// drops out of its subtree.  Each body therefore sees exactly the serial
+// reference's interaction list, in the reference's order (children 0..7,
+// depth first), and agrees with it to rounding, not just within the THETA
+// envelope.
+//
+// Acceptance is tested as border^2 < THETA^2 * dist^2 -- the reference's
+// border / dist < THETA (:405) without the FP64 divide and square root; the two
+// differ only when border/dist is within an ulp of THETA.
+constexpr int TRAV_WARPS = 4;
+constexpr int TRAV_STACK = 7 * (BH_MAX_LEVEL + 1) + 16; // <= 7 siblings pending per level + 8
+
+struct TravArgs {
+    const double4 *spos, *com;
+    const int *child;
+    const unsigned *first, *count, *perm, *own;
+    const unsigned char *level;
+    const double *bbox;
+    unsigned *flags;
+    unsigned long long *counters;
+    unsigned n_own_static; // used when own == nullptr (all bodies, identity list)
+    BhParams p;
+};
+
+// m * (r2)^(-3/2), the 7-operation cube of nb_direct_f64.cu
+__device__ __forceinline__ double bh_inv_r3_times_m(double r2, double m)
+{
+    const double y0 = rsqrt_approx_f64(r2);
+    const double y02 = y0 * y0;
+    const double e = fma(-r2, y02, 1.0);
+    const double pe = fma(1.875, e, 1.5);
+    const double q = e * pe;
+    const double my = m * y0;
+    const double u = y02 * my;
+    return fma(u, q, u);
+}
+
+__global__ void __launch_bounds__(TRAV_WARPS * 32) traverse_kernel(const TravArgs a)
+{
+    __shared__ int s_ent[TRAV_WARPS][TRAV_STACK];
+    __shared__ unsigned s_mask[TRAV_WARPS][TRAV_STACK];
+    __shared__ double s_border2[BH_MAX_LEVEL + 2];
+    if (threadIdx.x <= BH_MAX_LEVEL) {
+        double b = 2.0 * a.bbox[0]; // root border = max (serial/barnes-hut.c:470), halved per level
+        for (unsigned l = 0; l < threadIdx.x; ++l) b /= 2;
+        s_border2[threadIdx.x] = b * b;
+    }
+    __syncthreads();
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned n_own = a.own ? a.flags[2] : a.n_own_static;
+    const unsigned j = (blockIdx.x * TRAV_WARPS + warp) * 32 + lane;
+    const bool valid = j < n_own;
+    const unsigned k = valid ? (a.own ? a.own[j] : j) : 0u;
+    const double4 me = a.spos[k];
+    const double theta2 = a.p.theta * a.p.theta, eps2 = a.p.eps2;
+    double ax = 0, ay = 0, az = 0;
+    unsigned n_inter = 0, n_visit = 0;
+    int *ent = s_ent[warp];
+    unsigned *msk = s_mask[warp];
+    int sp = 0;
+    const unsigned all = __ballot_sync(0xffffffffu, valid);
+    if (all && a.p.n >= 2) { // a single body feels nothing (root needs >= 2 bodies)
+        if (lane == 0) { ent[0] = -2; msk[0] = all; }
+        sp = 1;
+    }
+    __syncwarp();
+    while (sp > 0) {
+        --sp;
+        const int e = ent[sp];
+        const unsigned M = msk[sp];
+        __syncwarp();
+        const bool in = (M >> lane) & 1u;
+        if (e >= 0) { // a body (leaf): calculate_acceleration, skipping the body itself (:411)
+            if (in && (unsigned)e != k) {
+                const double4 b = a.spos[e];
+                const double dx = b.x - me.x, dy = b.y - me.y, dz = b.z - me.z;
+                const double r2 = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)),
+                                                      __dmul_rn(dz, dz)), eps2);
+                const double s = bh_inv_r3_times_m(r2, b.w);
+                ax = fma(dx, s, ax); ay = fma(dy, s, ay); az = fma(dz, s, az);
+                ++n_inter; ++n_visit;
+            }
+            continue;
+        }
+        const unsigned nd = (unsigned)(-e - 2);
+        const double4 c = a.com[nd];
+        const unsigned lvl = a.level[nd];
+        const double dx = c.x - me.x, dy = c.y - me.y, dz = c.z - me.z;
+        const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+        const bool accept = in && (s_border2[lvl] < theta2 * d2);
+        if (in) ++n_visit;
+        if (accept) {
+            const double s = bh_inv_r3_times_m(__dadd_rn(d2, eps2), c.w);
+            ax = fma(dx, s, ax); ay = fma(dy, s, ay); az = fma(dz, s, az);
+            ++n_inter;
+        }
+        const unsigned O = __ballot_sync(0xffffffffu, in && !accept);
+        if (!O) continue;
+        if (lvl == BH_MAX_LEVEL) { // bucket: bodies sharing one finest cell, summed directly
+            const unsigned f = a.first[nd], cn = a.count[nd];
+            for (unsigned t = f; t < f + cn; ++t) {
+                if (((O >> lane) & 1u) && t != k) {
+                    const double4 b = a.spos[t];
+                    const double bx = b.x - me.x, by = b.y - me.y, bz = b.z - me.z;
+                    const double r2 = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(bx, bx), __dmul_rn(by, by)),
+                                                          __dmul_rn(bz, bz)), eps2);
+                    const double s = bh_inv_r3_times_m(r2, b.w);
+                    ax = fma(bx, s, ax); ay = fma(by, s, ay); az = fma(bz, s, az);
+                    ++n_inter;
+                }
+            }
+            continue;
+        }
+        const int ch = lane < 8 ? a.child[(size_t)nd * 8 + lane] : -1;
+        const unsigned vb = __ballot_sync(0xffffffffu, ch != -1);
+        const int nv = __popc(vb);
+        if (sp + nv > TRAV_STACK) { // cannot happen for depth <= BH_MAX_LEVEL; flagged, not silent
+            if (lane == 0) a.flags[1] = 1;
+            break;
+        }
+        if (ch != -1) { // reversed, so that child 0 is popped first
+            const int r = __popc(vb & ((1u << lane) - 1u));
+            ent[sp + nv - 1 - r] = ch;
+            msk[sp + nv - 1 - r] = O;
+        }
+        sp += nv;
+        __syncwarp();
+    }
+
+    if (a.p.count_visits && a.counters) {
+        unsigned long long ni = n_inter, nv = n_visit;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            ni += __shfl_xor_sync(0xffffffffu, ni, o);
+            nv += __shfl_xor_sync(0xffffffffu, nv, o);
+        }
+        if (lane == 0) { atomicAdd(&a.counters[0], ni); atomicAdd(&a.counters[1], nv); }
+    }
+    if (!valid) return;
+
+    // ---- epilogue: the direct-sum kernel's (nb_direct_f64.cu): kick2 / kick1 / drift
+    const unsigned idx = a.perm[k];
+    const BhParams &p = a.p;
+    const double a3[3] = {p.G * ax, p.G * ay, p.G * az};
+    if (p.flags & NB_F_STORE_ACC) p.acc[idx] = make_double4(a3[0], a3[1], a3[2], 0.0);
+    if (p.flags & (NB_F_KICK2 | NB_F_KICK1_DRIFT)) {
+        const double4 V = p.vel[idx];
+        double v3[3] = {V.x, V.y, V.z};
+        double x3[3] = {me.x, me.y, me.z};
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            if (p.flags & NB_F_KICK2) v3[c] = __dadd_rn(v3[c], __dmul_rn(__dmul_rn(a3[c], p.dt), 0.5));
+            if (p.flags & NB_F_KICK1_DRIFT) {
+                v3[c] = __dadd_rn(v3[c], __dmul_rn(__dmul_rn(a3[c], p.dt), 0.5));
+                x3[c] = __dadd_rn(x3[c], __dmul_rn(v3[c], p.dt));
+            }
+        }
+        p.vel[idx] = make_double4(v3[0], v3[1], v3[2], 0.0);
+        if (p.flags & NB_F_KICK1_DRIFT) {
+            double *qn = reinterpret_cast<double *>(p.q_next + idx);
+            qn[0] = x3[0]; qn[1] = x3[1]; qn[2] = x3[2]; // mass was placed at upload
+        }
+    }
+}
+
+__global__ void reset_kernel(unsigned *level_count, unsigned *flags, double *bbox, unsigned *first,
+                             unsigned *count, unsigned char *level, unsigned n,
+                             unsigned long long *counters, int reset_counters)
+{
+    if (threadIdx.x < BH_MAX_LEVEL + 2) level_count[threadIdx.x] = threadIdx.x == 0 ? 1u : 0u;
+    if (threadIdx.x == 0) {
+        bbox[0] = 0.0;
+        first[0] = 0;
+        count[0] = n;
+        level[0] = 0;
+        flags[2] = 0;
+        if (reset_counters) counters[0] = counters[1] = 0;
+    }
+}
+
+} // namespace
+
+// ------------------------------------------------------------------ host ----
+static unsigned bh_node_cap(unsigned n) { return 2u * n + 4096u; }
+
+size_t bh_bytes(unsigned n)
+{
+    const size_t cap = bh_node_cap(n), nn = n ? n : 1;
+    return nn * (2 * 8 + 2 * 4 + 32 + 4) + cap * (32 + 32 + 4 + 4 + 1) +
+           (size_t)256 * bh_sort_blocks(n) * 4 + 4096;
+}
+
+#define BH_TRY(call)                       \
+    do {                                   \
+        cudaError_t _e = (call);           \
+        if (_e != cudaSuccess) return _e;  \
+    } while (0)
+
+cudaError_t bh_alloc(BhTree *t, unsigned n)
+{
+    const size_t nn = n ? n : 1;
+    t->n = n;
+    t->node_cap = bh_node_cap(n);
+    t->sort_blocks = bh_sort_blocks(n);
+    for (int b = 0; b < 2; ++b) {
+        BH_TRY(cudaMalloc(&t->key[b], nn * sizeof(uint64_t)));
+        BH_TRY(cudaMalloc(&t->val[b], nn * sizeof(unsigned)));
+    }
+    BH_TRY(cudaMalloc(&t->spos, nn * sizeof(double4)));
+    BH_TRY(cudaMalloc(&t->own, nn * sizeof(unsigned)));
+    BH_TRY(cudaMalloc(&t->com, (size_t)t->node_cap * sizeof(double4)));
+    BH_TRY(cudaMalloc(&t->child, (size_t)t->node_cap * 8 * sizeof(int)));
+    BH_TRY(cudaMalloc(&t->first, (size_t)t->node_cap * sizeof(unsigned)));
+    BH_TRY(cudaMalloc(&t->count, (size_t)t->node_cap * sizeof(unsigned)));
+    BH_TRY(cudaMalloc(&t->level, (size_t)t->node_cap));
+    BH_TRY(cudaMalloc(&t->level_count, (BH_MAX_LEVEL + 2) * sizeof(unsigned)));
+    BH_TRY(cudaMalloc(&t->flags, 4 * sizeof(unsigned)));
+    BH_TRY(cudaMemset(t->flags, 0, 4 * sizeof(unsigned)));
+    BH_TRY(cudaMalloc(&t->bbox, 2 * sizeof(double)));
+    BH_TRY(cudaMalloc(&t->hist, (size_t)256 * t->sort_blocks * sizeof(unsigned)));
+    BH_TRY(cudaMalloc(&t->counters, 2 * sizeof(unsigned long long)));
+    BH_TRY(cudaMemset(t->counters, 0, 2 * sizeof(unsigned long long)));
+    return cudaSuccess;
+}
+
+void bh_free(BhTree *t)
+{
+    void *bufs[] = {t->key[0], t->key[1], t->val[0], t->val[1], t->spos, t->own, t->com, t->child,
+                    t->first, t->count, t->level, t->level_count, t->flags, t->bbox, t->hist,
+                    t->counters};
+    for (void *b : bufs)
+        if (b) cudaFree(b);
+    *t = BhTree();
+}
+
+cudaError_t bh_evaluate(BhTree *t, const BhParams &p, cudaStream_t s, unsigned *launches)
+{
+    const unsigned n = p.n;
+    unsigned nl = 0;
+    if (n == 0) return cudaSuccess;
+    const unsigned nblk = (n + BH_THREADS - 1) / BH_THREADS;
+    const unsigned wide = nblk < 148u * 8u ? nblk : 148u * 8u; // grid-stride kernels: 8 CTAs per SM
+    reset_kernel<<<1, 32, 0, s>>>(t->level_count, t->flags, t->bbox, t->first, t->count, t->level,
+                                  n, t->counters, p.count_visits);
+    bbox_kernel<<<wide, BH_THREADS, 0, s>>>(p.q_cur, n, reinterpret_cast<unsigned long long *>(t->bbox));
+    morton_kernel<<<nblk, BH_THREADS, 0, s>>>(p.q_cur, n, t->bbox, t->key[0], t->val[0]);
+    nl += 3;
+    BH_TRY(bh_radix_sort(t, n, 3 * BH_MAX_LEVEL, s, &nl));
+    gather_sorted_kernel<<<nblk, BH_THREADS, 0, s>>>(p.q_cur, t->val[0], n, t->spos);
+    ++nl;
+    const bool sliced = !(p.own_begin == 0 && p.own_end >= n);
+    if (sliced) {
+        own_list_kernel<<<1, 1024, 0, s>>>(t->val[0], n, p.own_begin, p.own_end, t->own, &t->flags[2]);
+        ++nl;
+    }
+    if (n >= 2) {
+        BuildArgs ba{t->key[0], t->first, t->count, t->level, t->child, t->level_count, t->flags,
+                     t->node_cap};
+        // a level holds at most n/2 nodes, 8 lanes each
+        const unsigned bgrid = min(wide, (n / 2 * 8 + BH_THREADS - 1) / BH_THREADS + 1);
+        for (int L = 0; L < BH_MAX_LEVEL; ++L) build_level_kernel<<<bgrid, BH_THREADS, 0, s>>>(ba, L);
+        const unsigned cgrid = min(wide, (n / 2 + BH_THREADS - 1) / BH_THREADS + 1);
+        for (int L = BH_MAX_LEVEL; L >= 0; --L)
+            com_level_kernel<<<cgrid, BH_THREADS, 0, s>>>(t->spos, t->child, t->first, t->count,
+                                                          t->level_count, t->com, L, t->node_cap);
+        nl += 2 * BH_MAX_LEVEL + 1;
+    }
+    TravArgs ta;
+    ta.spos = t->spos; ta.com = t->com; ta.child = t->child;
+    ta.first = t->first; ta.count = t->count; ta.perm = t->val[0];
+    ta.own = sliced ? t->own : nullptr;
+    ta.level = t->level; ta.bbox = t->bbox; ta.flags = t->flags; ta.counters = t->counters;
+    ta.n_own_static = n;
+    ta.p = p;
+    const unsigned max_own = sliced ? (p.own_end > p.own_begin ? min(p.own_end, n) - min(p.own_begin, n) : 0u) : n;
+    if (max_own) {
+        const unsigned tgrid = (max_own + TRAV_WARPS * 32 - 1) / (TRAV_WARPS * 32);
+        traverse_kernel<<<tgrid, TRAV_WARPS * 32, 0, s>>>(ta);
+        ++nl;
+    }
+    if (launches) *launches += nl;
+    return cudaGetLastError();
+}
+
+cudaError_t bh_stats(BhTree *t, BhStats *out, cudaStream_t s)
+{
+    unsigned lc[BH_MAX_LEVEL + 2], fl[4];
+    double bb[2];
+    unsigned long long cn[2];
+    BH_TRY(cudaMemcpyAsync(lc, t->level_count, sizeof(lc), cudaMemcpyDeviceToHost, s));
+    BH_TRY(cudaMemcpyAsync(fl, t->flags, sizeof(fl), cudaMemcpyDeviceToHost, s));
+    BH_TRY(cudaMemcpyAsync(bb, t->bbox, sizeof(double), cudaMemcpyDeviceToHost, s));
+    BH_TRY(cudaMemcpyAsync(cn, t->counters, sizeof(cn), cudaMemcpyDeviceToHost, s));
+    BH_TRY(cudaStreamSynchronize(s));
+    out->nodes = 0;
+    out->depth = 0;
+    for (int l = 0; l <= BH_MAX_LEVEL; ++l) {
+        out->nodes += lc[l];
+        if (lc[l]) out->depth = (unsigned)l + 1; // the reference counts the root as depth 1
+    }
+    out->pool_overflow = fl[0];
+    out->stack_overflow = fl[1];
+    out->root_border = 2.0 * bb[0];
+    out->interactions = cn[0];
+    out->visits = cn[1];
+    return cudaSuccess;
+}
+
+} // namespace nb

@@ -1,0 +1,80 @@
+// nb_bh.cuh -- Barnes-Hut force evaluation for sm_100a: Morton keys, radix
+// sort, level-wise octree build, bottom-up centre of mass, warp-cooperative
+// THETA traversal with a shared-memory stack (nb_bh.cu, nb_bh_sort.cu).
+//
+// Stands in for the reference's tree pipeline (serial/barnes-hut.c:114-434,
+// cuda/barnes-hut.cu:154-629).  The CELL SET is the reference's: cube
+// [-max/2, max/2]^3 centred on the origin with max = 2 max|coord|
+// (serial/barnes-hut.c:326-338), octant rule `>=` goes high, index z*4+y*2+x
+// (:114-133), a branch exists iff its cell holds >= 2 bodies, a leaf is one
+// body; the reference inserts bodies one by one with locks, here the same
+// cells come out of a sort.  FP64 throughout, like the reference.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace nb {
+
+constexpr int BH_MAX_LEVEL = 21; // 3 x 21 = 63 key bits; deeper cells become buckets
+
+// Device buffers of one engine's tree.  Bodies are referred to by their rank k
+// in Morton order ("sorted index"); perm[k] is the body's index in the state
+// arrays.
+struct BhTree {
+    unsigned n = 0;        // real bodies
+    unsigned node_cap = 0; // internal-node pool size
+    // per body
+    uint64_t *key[2] = {nullptr, nullptr}; // Morton keys, ping-pong for the sort
+    unsigned *val[2] = {nullptr, nullptr}; // body index, ping-pong; val[0] ends as perm
+    double4 *spos = nullptr;               // x,y,z,m in Morton order
+    unsigned *own = nullptr;               // sorted indices this rank integrates, Morton order
+    // per internal node
+    double4 *com = nullptr;   // centre of mass x,y,z + total mass
+    int *child = nullptr;     // [node][8]: -1 empty, >= 0 body (sorted index), <= -2 node -(c+2)
+    unsigned *first = nullptr, *count = nullptr; // the node's bodies: sorted range
+    unsigned char *level = nullptr;              // depth (root = 0)
+    // bookkeeping (device)
+    unsigned *level_count = nullptr; // [BH_MAX_LEVEL + 2] nodes per level
+    unsigned *flags = nullptr;       // [0] node-pool overflow, [1] stack overflow, [2] own count
+    double *bbox = nullptr;          // [0] max |coord| (as ordered bits during the reduction)
+    // radix-sort scratch
+    unsigned *hist = nullptr; // [256][sort_blocks]
+    unsigned sort_blocks = 0;
+    // visit counters for the bench (optional): [0] interactions, [1] node visits
+    unsigned long long *counters = nullptr;
+};
+
+struct BhParams {
+    const double4 *q_cur; // positions + mass, state order (all bodies)
+    double4 *q_next;      // next positions (bodies of this rank written)
+    double4 *vel;         // velocities, state order
+    double4 *acc;         // stored accelerations, state order, or nullptr
+    unsigned n;           // real bodies
+    unsigned own_begin, own_end; // state-order slice integrated by this rank
+    unsigned flags;       // NB_F_* of nb_common.cuh
+    double dt, eps2, G, theta;
+    int count_visits;     // 1: accumulate tree.counters
+};
+
+size_t bh_bytes(unsigned n);
+cudaError_t bh_alloc(BhTree *t, unsigned n);
+void bh_free(BhTree *t);
+// One force evaluation: bbox -> keys -> sort -> build -> COM -> traversal with the
+// kick/drift epilogue selected by p.flags.  Returns the number of kernel launches
+// through *launches.
+cudaError_t bh_evaluate(BhTree *t, const BhParams &p, cudaStream_t s, unsigned *launches);
+// tree statistics of the last evaluation (host sync): internal nodes, depth,
+// root border, overflow flags
+struct BhStats {
+    unsigned nodes, depth, pool_overflow, stack_overflow;
+    double root_border;
+    unsigned long long interactions, visits;
+};
+cudaError_t bh_stats(BhTree *t, BhStats *out, cudaStream_t s);
+
+// stable LSD radix sort of (key, val) pairs on 8-bit digits (nb_bh_sort.cu);
+// result in key[0], val[0].  bits: number of low key bits that matter.
+cudaError_t bh_radix_sort(BhTree *t, unsigned n, int bits, cudaStream_t s, unsigned *launches);
+unsigned bh_sort_blocks(unsigned n);
+
+} // namespace nb

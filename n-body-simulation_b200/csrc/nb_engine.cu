@@ -23,6 +23,7 @@
 
 #include "../../include/nbody_engine.h"
 #include "nb_aux.cuh"
+#include "nb_bh.cuh"
 #include "nb_direct.cuh"
 
 using namespace nb;
@@ -125,6 +126,9 @@ struct nb_engine {
     double *stage_pos = nullptr, *stage_vel = nullptr; // host-packing staging, n*4 / n*3 doubles
     double *energy_part = nullptr;
     DirectPlan plan;
+    BhTree tree;            // NB_ALGO_BARNES_HUT only
+    bool bh = false;
+    bool count_visits = false;
     State state = SYNCED_NOACC;
     void *comm = nullptr;
     bool vel_complete = true; // world > 1: do all ranks hold all velocities?
@@ -200,7 +204,24 @@ int launch_force(nb_engine *e, unsigned flags)
     p.G = e->cfg.G;
     NB_CUDA(cudaEventRecord(e->ev_f0, e->stream));
     int rc;
-    if (e->gather_pending && e->plan.can_split && !(e->cfg.tune_flags & NB_TUNE_NO_OVERLAP)) {
+    if (e->bh) {
+        // the tree is built from everybody's positions: no own-slice head start here
+        if ((rc = wait_gather(e))) return rc;
+        BhParams bp;
+        bp.q_cur = static_cast<const double4 *>(p.q_cur);
+        bp.q_next = static_cast<double4 *>(p.q_next);
+        bp.vel = static_cast<double4 *>(p.vel);
+        bp.acc = static_cast<double4 *>(p.acc);
+        bp.n = (unsigned)e->n;
+        bp.own_begin = e->i_begin;
+        bp.own_end = e->i_end;
+        bp.flags = flags;
+        bp.dt = p.dt; bp.eps2 = p.eps2; bp.G = p.G; bp.theta = e->cfg.theta;
+        bp.count_visits = e->count_visits ? 1 : 0;
+        unsigned nl = 0;
+        NB_CUDA(bh_evaluate(&e->tree, bp, e->stream, &nl));
+        e->st.kernel_launches += nl;
+    } else if (e->gather_pending && e->plan.can_split && !(e->cfg.tune_flags & NB_TUNE_NO_OVERLAP)) {
         // positions of the other ranks are still in flight: start on the own slice
         StepParams a = p;
         a.flags = NB_F_PARTIAL_OUT;
@@ -216,8 +237,9 @@ int launch_force(nb_engine *e, unsigned flags)
     NB_CUDA(cudaEventRecord(e->ev_f1, e->stream));
     e->have_force_ev = true;
     e->st.force_launches++;
-    e->st.interactions += (unsigned long long)(e->i_end - e->i_begin) * e->unit_bodies *
-                          (unsigned long long)e->n_units * e->unit_bodies;
+    if (!e->bh) // direct sum: every ordered pair; Barnes-Hut counts on the device (nb_tree_stats)
+        e->st.interactions += (unsigned long long)(e->i_end - e->i_begin) * e->unit_bodies *
+                              (unsigned long long)e->n_units * e->unit_bodies;
     if (flags & (NB_F_KICK2 | NB_F_KICK1_DRIFT)) e->vel_complete = (e->cfg.world <= 1);
     if (flags & NB_F_KICK1_DRIFT) {
         int rc = all_gather_units(e, e->q[e->cur ^ 1], e->unit_bytes);
@@ -332,6 +354,7 @@ void nb_free(nb_engine *e)
     if (e->comm_stream) cudaStreamSynchronize(e->comm_stream);
     if (e->stream) cudaStreamSynchronize(e->stream);
     if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
+    bh_free(&e->tree);
     void *bufs[] = {e->q[0], e->q[1], e->vel, e->acc, e->workspace, e->partial, e->counters,
                     e->stage_pos, e->stage_vel, e->energy_part};
     for (void *b : bufs)
@@ -405,6 +428,9 @@ static int init_impl(nb_engine *e, const double *pos, const double *vel)
     NB_CUDA(cudaMemsetAsync(e->acc, 0, vbytes, e->stream));
     NB_CUDA(cudaMalloc(&e->workspace, e->plan.workspace_bytes ? e->plan.workspace_bytes : 16));
     if (e->plan.partial_bytes) NB_CUDA(cudaMalloc(&e->partial, e->plan.partial_bytes));
+    e->bh = c.algorithm == NB_ALGO_BARNES_HUT;
+    e->count_visits = (c.tune_flags & NB_TUNE_COUNT_VISITS) != 0;
+    if (e->bh) NB_CUDA(bh_alloc(&e->tree, (unsigned)e->n));
     NB_CUDA(cudaMalloc(&e->counters, e->plan.counter_bytes ? e->plan.counter_bytes : 16));
     NB_CUDA(cudaMemsetAsync(e->counters, 0, e->plan.counter_bytes ? e->plan.counter_bytes : 16,
                             e->stream));
@@ -450,8 +476,16 @@ int nb_init(nb_engine **out, const nb_config *cfg, size_t n, const double *pos_x
         set_err("nb_init", "bad configuration");
         return NB_E_INVALID;
     }
-    if (cfg->algorithm != NB_ALGO_DIRECT) {
-        set_err("nb_init", "algorithm not available in this build");
+    if (cfg->algorithm != NB_ALGO_DIRECT && cfg->algorithm != NB_ALGO_BARNES_HUT) {
+        set_err("nb_init", "unknown algorithm");
+        return NB_E_INVALID;
+    }
+    if (cfg->algorithm == NB_ALGO_BARNES_HUT && cfg->precision != NB_PREC_FP64) {
+        set_err("nb_init", "Barnes-Hut runs in FP64 (the reference's precision) only");
+        return NB_E_INVALID;
+    }
+    if (cfg->algorithm == NB_ALGO_BARNES_HUT && !(cfg->theta >= 0)) {
+        set_err("nb_init", "bad theta");
         return NB_E_INVALID;
     }
     int ndev = nb_device_count();
@@ -552,6 +586,11 @@ int nb_gather(nb_engine *e, double *pos_xyzm, double *vel_xyz)
                                     cudaMemcpyDeviceToHost, e->stream));
     }
     NB_CUDA(cudaStreamSynchronize(e->stream));
+    if (e->bh && e->st.force_launches) { // a truncated tree must not pass for a result
+        nb_tree_info ti;
+        rc = nb_tree_stats(e, &ti);
+        if (rc) return rc;
+    }
     return NB_OK;
 }
 
@@ -612,6 +651,31 @@ int nb_energy(nb_engine *e, double *KE, double *PE)
     free(h);
     *KE = 0.5 * ke;
     *PE = -e->cfg.G * pe;
+    return NB_OK;
+}
+
+int nb_tree_stats(nb_engine *e, nb_tree_info *out)
+{
+    if (!e || !out) return NB_E_INVALID;
+    if (!e->bh) {
+        set_err("nb_tree_stats", "engine was not created with NB_ALGO_BARNES_HUT");
+        return NB_E_STATE;
+    }
+    int rc = set_device(e);
+    if (rc) return rc;
+    BhStats bs;
+    NB_CUDA(bh_stats(&e->tree, &bs, e->stream));
+    out->nodes = bs.nodes;
+    out->depth = bs.depth;
+    out->root_border = bs.root_border;
+    out->interactions = bs.interactions;
+    out->node_visits = bs.visits;
+    out->pool_overflow = (int)bs.pool_overflow;
+    out->stack_overflow = (int)bs.stack_overflow;
+    if (bs.pool_overflow || bs.stack_overflow) {
+        set_err("nb_tree_stats", bs.pool_overflow ? "octree node pool exhausted" : "traversal stack overflow");
+        return NB_E_NOMEM;
+    }
     return NB_OK;
 }
 

@@ -19,12 +19,12 @@ HOST_LIB_PATH = os.path.join(HERE, "libnbhost.so")
 PREC_FP64, PREC_FP32 = 0, 1
 ALGO_DIRECT, ALGO_BARNES_HUT = 0, 1
 COMM_ID_BYTES = 128
-TUNE_SCALAR_FP32, TUNE_NO_SPLIT, TUNE_NO_OVERLAP = 1, 2, 4
+TUNE_SCALAR_FP32, TUNE_NO_SPLIT, TUNE_NO_OVERLAP, TUNE_COUNT_VISITS = 1, 2, 4, 8
 SLICE_ALIGN = {PREC_FP32: 64, PREC_FP64: 128}  # units; nb_direct.cuh kSliceAlign*
 
 # every symbol include/nbody_engine.h declares
 ABI_SYMBOLS = ["nb_config_default", "nb_init", "nb_upload", "nb_step", "nb_gather",
-               "nb_accelerations", "nb_energy", "nb_sync", "nb_get_stats", "nb_free",
+               "nb_accelerations", "nb_energy", "nb_sync", "nb_get_stats", "nb_tree_stats", "nb_free",
                "nb_comm_id", "nb_strerror", "nb_last_error", "nb_device_count", "nb_version"]
 HOST_SYMBOLS = ["nbh_read_bodies", "nbh_parse_bodies", "nbh_free", "nbh_parse_times",
                 "nbh_write_frame", "nbh_format_frame", "nbh_format_lf", "nbh_write_bodies"]
@@ -45,6 +45,12 @@ class NbStats(C.Structure):
                 ("n", C.c_size_t), ("n_padded", C.c_size_t), ("slice_begin", C.c_size_t),
                 ("slice_end", C.c_size_t), ("collectives", C.c_ulonglong),
                 ("split_evaluations", C.c_ulonglong)]
+
+
+class NbTreeInfo(C.Structure):
+    _fields_ = [("nodes", C.c_uint), ("depth", C.c_uint), ("root_border", C.c_double),
+                ("interactions", C.c_ulonglong), ("node_visits", C.c_ulonglong),
+                ("pool_overflow", C.c_int), ("stack_overflow", C.c_int)]
 
 
 class NbodyError(RuntimeError):
@@ -78,6 +84,7 @@ def load_library():
     lib.nb_energy.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.nb_sync.argtypes = [C.c_void_p]
     lib.nb_get_stats.argtypes = [C.c_void_p, C.POINTER(NbStats)]
+    lib.nb_tree_stats.argtypes = [C.c_void_p, C.POINTER(NbTreeInfo)]
     lib.nb_free.argtypes = [C.c_void_p]
     lib.nb_free.restype = None
     lib.nb_comm_id.argtypes = [C.c_void_p, C.c_size_t]
@@ -213,6 +220,11 @@ class Engine:
         st = NbStats()
         _check(self.lib, self.lib.nb_get_stats(self.handle, C.byref(st)), "nb_get_stats")
         return st
+
+    def tree_stats(self):
+        ti = NbTreeInfo()
+        _check(self.lib, self.lib.nb_tree_stats(self.handle, C.byref(ti)), "nb_tree_stats")
+        return ti
 
     def close(self):
         if self.handle:
