@@ -19,6 +19,8 @@ nb = load_package()
 def run(spec):
     parts = spec.split(":")
     prec = nb.PREC_FP32 if parts[0] == "fp32" else nb.PREC_FP64
+    algo = nb.ALGO_BARNES_HUT if parts[0] == "bh" else nb.ALGO_DIRECT
+    plummer = False
     n = int(parts[1])
     opts = parts[2].split(",") if len(parts) > 2 else []
     flags, ctas, steps = 0, 0, 3
@@ -33,10 +35,18 @@ def run(spec):
             flags |= int(o[8:]) << 8
         elif o.startswith("steps="):
             steps = int(o[6:])
+        elif o == "count":
+            flags |= nb.TUNE_COUNT_VISITS
+        elif o == "plummer":
+            plummer = True
     rng = np.random.default_rng(17)
     pm = np.concatenate([rng.standard_normal((n, 3)), np.full((n, 1), 1.0 / n)], axis=1)
     vel = np.zeros((n, 3))
-    with nb.Engine(pm, vel, precision=prec, ctas_per_sm=ctas, tune_flags=flags) as e:
+    if plummer:
+        sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+        from bench import plummer as gen
+        pm, vel = gen(n)
+    with nb.Engine(pm, vel, precision=prec, algorithm=algo, ctas_per_sm=ctas, tune_flags=flags) as e:
         e.step(2)  # warm-up
         e.sync()
         times = []
@@ -50,6 +60,11 @@ def run(spec):
                "force_ms_min": best, "force_ms_med": med,
                "interactions_per_s": n * float(st.n_padded) / (med * 1e-3),
                "frac_fp32_roofline_20flop_1965MHz": n * float(st.n_padded) / (med * 1e-3) / 3.72e12}
+        if algo == nb.ALGO_BARNES_HUT:
+            ti = e.tree_stats()
+            out.update({"nodes": ti.nodes, "depth": ti.depth, "interactions_per_body": ti.interactions / n,
+                        "visits_per_body": ti.node_visits / n, "launches_per_eval": None})
+            del out["frac_fp32_roofline_20flop_1965MHz"], out["interactions_per_s"]
     print(json.dumps(out), flush=True)
 
 
