@@ -14,6 +14,11 @@
  * Like the reference, the frame file is written only by the RESULTS build
  * (exh_cuda_results; the reference's *_debug targets, Makefile:17-18) or when
  * NB_RESULTS=1 is set; otherwise the output name is accepted and ignored.
+ * Compiled with -DNB_BARNES_HUT this is barnes-hut-cuda (cuda/barnes-hut.cu:814-1186):
+ * the same five arguments, the THETA = 0.5 octree evaluation in place of the
+ * direct sum, and -- as in that program, which force-defines RESULTS (:50) and
+ * writes its first frame after the first drift (:1064) -- the frame file is
+ * written by default and carries n_steps frames, no initial one.
  * Optional knobs (environment, so the reference command line is unchanged):
  *   NB_PRECISION=fp64|fp32 (default fp64, the reference's precision)
  *   NB_DEVICE=<ordinal>    NB_CHECKPOINT=<file>: final state in INPUT format
@@ -63,9 +68,13 @@ int main(int argc, char *argv[])
     printf("Start: %f, end: %f, delta time: %f, time steps: %d, ents: %d\n", start, end, dt,
            n_steps, (int)n_ents);
 
-    int results = 0;
+    int results = 0, initial_frame = 1;
 #ifdef RESULTS
     results = 1;
+#endif
+#ifdef NB_BARNES_HUT
+    results = 1;
+    initial_frame = 0;
 #endif
     const char *env = getenv("NB_RESULTS");
     if (env)
@@ -74,6 +83,9 @@ int main(int argc, char *argv[])
     nb_config cfg;
     nb_config_default(&cfg);
     cfg.dt = (double)dt; /* the float promoted to double, cuda/exhaustive.cu:38,56 */
+#ifdef NB_BARNES_HUT
+    cfg.algorithm = NB_ALGO_BARNES_HUT; /* FP64 only, like the reference */
+#endif
     env = getenv("NB_PRECISION");
     if (env && strcmp(env, "fp32") == 0)
         cfg.precision = NB_PREC_FP32;
@@ -96,7 +108,8 @@ int main(int argc, char *argv[])
             fprintf(stderr, "Error opening file '%s'\n", argv[5]);
             exit(1);
         }
-        nbh_write_frame(fpt, n_ents, positions); /* frame 0 = initial state */
+        if (initial_frame)
+            nbh_write_frame(fpt, n_ents, positions); /* frame 0 = initial state */
         for (int t = 0; t < n_steps; t++) {
             if ((rc = nb_step(eng, 1)))
                 die_engine("nb_step", rc);
@@ -123,7 +136,7 @@ int main(int argc, char *argv[])
     printf("Elapsed wall time: %f s\n", time_spent);
 
     nb_stats st;
-    if (nb_get_stats(eng, &st) == NB_OK && time_spent > 0)
+    if (nb_get_stats(eng, &st) == NB_OK && time_spent > 0 && cfg.algorithm == NB_ALGO_DIRECT)
         printf("Pairwise interactions: %llu (%.3e /s), force launches: %llu\n", st.interactions,
                (double)st.interactions / time_spent, st.force_launches);
     nb_free(eng);

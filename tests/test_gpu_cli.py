@@ -1,0 +1,126 @@
+"""The C host programs end to end on a GPU: the reference's command line in, the
+reference's frame file and stdout out.
+
+Reference material: tests/golden/programs.npz holds md5 / line count / head / tail / stdout
+of the frame file written by the reference's own exh_serial and exh_mp (-DRESULTS) for
+BASELINE config 1 (`tests/1k_bodies.csv 0 1 0.01`).  The frame file has 6 decimals, the
+engine agrees with the reference to ~1e-10 after 100 steps, so the files are expected to be
+byte-identical; the numeric comparison (1e-6 absolute) is the contract, the md5 the bonus.
+"""
+import hashlib
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, golden
+
+pytestmark = pytest.mark.gpu
+BIN = os.path.join(ROOT, "n-body-simulation_b200", "bin")
+
+
+def write_csv(tmp_path, name):
+    """the fixture in the reference's input format (x,y,z,vx,vy,vz,mass); %.17g round-trips the
+    doubles the reference's reader produced from tests/<name>.csv"""
+    g = golden(name)
+    p = tmp_path / (name + ".csv")
+    rows = np.concatenate([g["pos_xyzm"][:, :3], g["vel"], g["pos_xyzm"][:, 3:4]], axis=1)
+    p.write_text("".join(",".join("%.17g" % x for x in r) + "\n" for r in rows))
+    return str(p)
+
+
+def run(prog, *args, env=None):
+    e = dict(os.environ)
+    e.update(env or {})
+    return subprocess.run([os.path.join(BIN, prog)] + [str(a) for a in args], env=e,
+                          capture_output=True, text=True, timeout=300)
+
+
+def frames(path):
+    return np.loadtxt(path, delimiter=",")
+
+
+def test_exh_cuda_results_matches_reference_frame_file(tmp_path):
+    ref = golden("programs")
+    inp, out = write_csv(tmp_path, "1k_bodies"), str(tmp_path / "out.csv")
+    r = run("exh_cuda_results", inp, 0, 1, 0.01, out)
+    assert r.returncode == 0, r.stderr
+    lines = r.stdout.splitlines()
+    # reference: "Start: 0.000000, end: 1.000000, delta time: 0.010000, time steps: 100, ents: 1000"
+    assert lines[0].startswith("Start: 0.000000, end: 1.000000, delta time: 0.010000, "
+                               "time steps: 100, ents: 1000")
+    assert lines[1] == "Completed. Output file: " + out
+    assert lines[2].startswith("Elapsed wall time: ") and lines[2].endswith(" s")
+    data = open(out, "rb").read()
+    text = data.decode().splitlines()
+    assert len(text) == int(ref["exh_serial_results_lines"]) == 101 * 1000
+    # head / tail were cut by bytes: drop the broken line at the cut
+    head = str(ref["exh_serial_results_head"]).splitlines()[:-1]
+    tail = str(ref["exh_serial_results_tail"]).splitlines()[1:]
+    assert text[:len(head)] == head
+    got_tail = np.array([[float(x) for x in ln.split(",")] for ln in text[-len(tail):]])
+    want_tail = np.array([[float(x) for x in ln.split(",")] for ln in tail])
+    assert np.abs(got_tail - want_tail).max() <= 1e-6
+    assert hashlib.md5(data).hexdigest() == str(ref["exh_serial_results_md5"])
+
+
+def test_exh_cuda_five_frames_and_old_argv(tmp_path):
+    """grid_size / block_size of the reference's exh_cuda are accepted and ignored"""
+    ref = str(golden("programs")["frames_100_bodies_g1_5steps"]).splitlines()
+    inp, out = write_csv(tmp_path, "100_bodies_g1"), str(tmp_path / "o.csv")
+    r = run("exh_cuda_results", inp, 0, 0.05, 0.01, out, 4, 128)
+    assert r.returncode == 0, r.stderr
+    got = open(out).read().splitlines()
+    assert len(got) == len(ref)
+    a = np.array([[float(x) for x in ln.split(",")] for ln in got])
+    b = np.array([[float(x) for x in ln.split(",")] for ln in ref])
+    assert np.abs(a - b).max() <= 1e-6
+    assert got == ref
+
+
+def test_exh_cuda_without_results_ignores_output_name(tmp_path):
+    inp, out = write_csv(tmp_path, "33_bodies"), str(tmp_path / "never.csv")
+    r = run("exh_cuda", inp, 0, 0.1, 0.01, out)
+    assert r.returncode == 0 and not os.path.exists(out)
+    assert "time steps: 10, ents: 33" in r.stdout      # float step count (serial/exhaustive.c:53)
+    r = run("exh_cuda", inp, 0, 0.1, 0.01, out, env={"NB_PRECISION": "fp32", "NB_RESULTS": "1"})
+    assert r.returncode == 0 and len(open(out).read().splitlines()) == 11 * 33
+
+
+def test_checkpoint_restarts_bitwise(tmp_path):
+    """NB_CHECKPOINT writes the final state in INPUT format (%.17g): 6 steps == 3 + 3 steps."""
+    inp = write_csv(tmp_path, "100_bodies_g1")
+    a, b, c = (str(tmp_path / n) for n in ("a.csv", "b.csv", "c.csv"))
+    dt = 0.015625  # 1/64: step counts are exact in the reference's float arithmetic
+    assert run("exh_cuda", inp, 0, 6 * dt, dt, "x", env={"NB_CHECKPOINT": a}).returncode == 0
+    assert run("exh_cuda", inp, 0, 3 * dt, dt, "x", env={"NB_CHECKPOINT": b}).returncode == 0
+    assert run("exh_cuda", b, 3 * dt, 6 * dt, dt, "x", env={"NB_CHECKPOINT": c}).returncode == 0
+    assert open(a).read() == open(c).read()
+
+
+def test_error_exits(tmp_path):
+    inp = write_csv(tmp_path, "10_bodies")
+    r = run("exh_cuda", inp, 0, 1)
+    assert r.returncode == 1 and "Usage" in r.stderr
+    r = run("exh_cuda", str(tmp_path / "missing.csv"), 0, 1, 0.01, "o")
+    assert r.returncode == 1 and "Error opening file" in r.stderr
+    bad = tmp_path / "bad.csv"
+    bad.write_text("1,2,3,4,5,6,7\n1,2,three,4,5,6,7\n")
+    r = run("exh_cuda", str(bad), 0, 1, 0.01, "o")
+    assert r.returncode == 1 and "not well formed" in r.stderr
+
+
+def test_barnes_hut_cuda_program(tmp_path, oracle_lib):
+    """barnes-hut-cuda: frames after every drift, no initial frame (cuda/barnes-hut.cu:1064)"""
+    g = golden("100_bodies_g1")
+    inp, out = write_csv(tmp_path, "100_bodies_g1"), str(tmp_path / "bh.csv")
+    r = run("barnes-hut-cuda", inp, 0, 0.05, 0.01, out)
+    assert r.returncode == 0, r.stderr
+    f = frames(out)
+    assert f.shape == (5 * 100, 5)
+    pm, v = g["pos_xyzm"].copy(), g["vel"].copy()
+    oracle_lib.orc_bh_propagate(100, pm, v, 5, np.float32(0.01))
+    last = f[-100:]
+    assert np.array_equal(last[:, 0], np.arange(100))
+    assert np.abs(last[:, 1:4] - pm[:, :3]).max() <= 1e-6 and np.abs(last[:, 4] - pm[:, 3]).max() <= 1e-6
