@@ -200,11 +200,7 @@ def run_gpu_arm(args):
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
         # rank 0 creates the engine communicator id; torch.distributed carries it
-        idt = torch.zeros(nb.COMM_ID_BYTES, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            idt.copy_(torch.frombuffer(bytearray(nb.comm_id()), dtype=torch.uint8))
-        dist.broadcast(idt, 0)
-        comm = bytes(idt.cpu().numpy().tobytes())
+        comm = nb.share_comm_id(dist, rank, device="cuda")
 
     def barrier():
         if dist is not None:

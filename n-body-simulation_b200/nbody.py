@@ -137,6 +137,18 @@ def comm_id():
     return buf.raw
 
 
+def share_comm_id(dist, rank, device="cpu", make=None):
+    """Rank 0 creates the engine communicator id, torch.distributed carries it to the others
+    (the host-side half of the multi-GPU plumbing; works over gloo and nccl)."""
+    import torch
+    idt = torch.zeros(COMM_ID_BYTES, dtype=torch.uint8, device=device)
+    if rank == 0:
+        raw = (make or comm_id)()
+        idt.copy_(torch.frombuffer(bytearray(raw), dtype=torch.uint8))
+    dist.broadcast(idt, 0)
+    return bytes(idt.cpu().numpy().tobytes())
+
+
 def slice_bounds(n, world, rank, precision):
     """The engine's i-slice ownership rule, mirrored for the host side (bodies).
 
