@@ -294,6 +294,15 @@ def run_gpu_arm(args):
                 "peak_source": "nominal: 148 SM x 128 FP32 lanes x 2 x 1965 MHz "
                                "(MEASURED_PEAKS.json has no FP32 FMA figure; sm_max_mhz from it)",
                 "flop_per_interaction": FLOP_PER_INTERACTION,
+                # tools/microbench.cu on this pool's B200 (profiles/r1_microbench_pipe_rates.jsonl):
+                # FFMA 123.1 lane-ops/clk/SM; 6 FFMA2 + 1 MUFU (this kernel's mix) 12.5 clk per
+                # interaction-warp -> the mix's ceiling at sm_max_mhz
+                "peak_measured_ffma": SM_COUNT * 123.09 * 2 * SM_MAX_MHZ * 1e6 / 1e12,
+                "ceiling_of_instruction_mix": (SM_COUNT * 4 * 32 / 12.5 * SM_MAX_MHZ * 1e6
+                                               * FLOP_PER_INTERACTION / 1e12) if prec == nb.PREC_FP32
+                else (SM_COUNT * 62.2 / 16.0 * SM_MAX_MHZ * 1e6 * FLOP_PER_INTERACTION / 1e12),
+                "traffic_note": "ncu dram__bytes_read+write per launch: profiles/ (kernel is FMA-bound, "
+                                "HBM traffic ~1e-4 of the time budget)",
                 "hbm_algorithmic_bytes_per_launch": 64.0 * my_rows if prec == nb.PREC_FP32
                 else 128.0 * my_rows}
         if clocks and clocks.get("sm_mhz"):

@@ -293,8 +293,7 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32) traverse_kernel(const TravArg
             if (in && (unsigned)e != k) {
                 const double4 b = a.spos[e];
                 const double dx = b.x - me.x, dy = b.y - me.y, dz = b.z - me.z;
-                const double r2 = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)),
-                                                      __dmul_rn(dz, dz)), eps2);
+                const double r2 = fma(dz, dz, fma(dy, dy, fma(dx, dx, eps2)));
                 const double s = bh_inv_r3_times_m(r2, b.w);
                 ax = fma(dx, s, ax); ay = fma(dy, s, ay); az = fma(dz, s, az);
                 ++n_inter; ++n_visit;
@@ -305,11 +304,13 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32) traverse_kernel(const TravArg
         const double4 c = a.com[nd];
         const unsigned lvl = a.level[nd];
         const double dx = c.x - me.x, dy = c.y - me.y, dz = c.z - me.z;
-        const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+        // |d|^2 with FMAs: 1 ulp off the reference's mul/add form (:101-104), which moves an
+        // accept/open decision only if border/dist sits within an ulp of THETA
+        const double d2 = fma(dz, dz, fma(dy, dy, dx * dx));
         const bool accept = in && (s_border2[lvl] < theta2 * d2);
         if (in) ++n_visit;
         if (accept) {
-            const double s = bh_inv_r3_times_m(__dadd_rn(d2, eps2), c.w);
+            const double s = bh_inv_r3_times_m(d2 + eps2, c.w);
             ax = fma(dx, s, ax); ay = fma(dy, s, ay); az = fma(dz, s, az);
             ++n_inter;
         }
@@ -321,8 +322,7 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32) traverse_kernel(const TravArg
                 if (((O >> lane) & 1u) && t != k) {
                     const double4 b = a.spos[t];
                     const double bx = b.x - me.x, by = b.y - me.y, bz = b.z - me.z;
-                    const double r2 = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(bx, bx), __dmul_rn(by, by)),
-                                                          __dmul_rn(bz, bz)), eps2);
+                    const double r2 = fma(bz, bz, fma(by, by, fma(bx, bx, eps2)));
                     const double s = bh_inv_r3_times_m(r2, b.w);
                     ax = fma(bx, s, ax); ay = fma(by, s, ay); az = fma(bz, s, az);
                     ++n_inter;
@@ -436,7 +436,7 @@ cudaError_t bh_alloc(BhTree *t, unsigned n)
     BH_TRY(cudaMalloc(&t->flags, 4 * sizeof(unsigned)));
     BH_TRY(cudaMemset(t->flags, 0, 4 * sizeof(unsigned)));
     BH_TRY(cudaMalloc(&t->bbox, 2 * sizeof(double)));
-    BH_TRY(cudaMalloc(&t->hist, (size_t)256 * t->sort_blocks * sizeof(unsigned)));
+    BH_TRY(cudaMalloc(&t->hist, ((size_t)256 * t->sort_blocks + 256) * sizeof(unsigned)));
     BH_TRY(cudaMalloc(&t->counters, 2 * sizeof(unsigned long long)));
     BH_TRY(cudaMemset(t->counters, 0, 2 * sizeof(unsigned long long)));
     return cudaSuccess;

@@ -7,7 +7,8 @@
 //
 // One pass = three launches:
 //   digit_histogram : per 2048-key tile, 256 bin counts -> hist[bin][tile]
-//   exclusive_scan  : over hist in (bin, tile) order -> global base of every (bin, tile)
+//   scan_rows       : CTA d scans row d of hist (tile order) and reports the row total;
+//                     the 256 totals are scanned inside scatter -> base of every (bin, tile)
 //   scatter         : re-reads the tile; a warp owns 256 consecutive keys and ranks
 //                     them 32 at a time with __match_any_sync, so equal digits keep
 //                     their input order (tile, warp, round, lane) = stable.
@@ -40,42 +41,74 @@ __global__ void __launch_bounds__(SORT_THREADS)
     hist[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
 }
 
-// Exclusive prefix sum of `len` counters in place, one CTA of 1024 threads: each
-// thread owns a contiguous chunk, the chunk totals are scanned in shared memory.
-__global__ void __launch_bounds__(1024) exclusive_scan(unsigned *__restrict__ a, unsigned len)
+// Row d of hist (the counts of digit d in every tile, tile order) is scanned in
+// place by CTA d; the row total goes to totals[d].  The offset of the row itself
+// (all smaller digits) is added by the scatter kernel from the 256 totals.
+__global__ void __launch_bounds__(1024)
+    scan_rows(unsigned *__restrict__ hist, unsigned nblocks, unsigned *__restrict__ totals)
 {
-    __shared__ unsigned part[1024];
-    const unsigned chunk = (len + 1023u) / 1024u;
-    const unsigned b = threadIdx.x * chunk;
-    const unsigned e = min(b + chunk, len);
-    unsigned s = 0;
-    for (unsigned i = b; i < e; ++i) s += a[i];
-    part[threadIdx.x] = s;
+    __shared__ unsigned wsum[32];
+    __shared__ unsigned carry;
+    unsigned *row = hist + (size_t)blockIdx.x * nblocks;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) carry = 0;
     __syncthreads();
-    // Hillis-Steele over 1024 partials
-    for (unsigned d = 1; d < 1024; d <<= 1) {
-        const unsigned v = threadIdx.x >= d ? part[threadIdx.x - d] : 0u;
+    for (unsigned b0 = 0; b0 < nblocks; b0 += 1024) {
+        const unsigned i = b0 + threadIdx.x;
+        const unsigned v = i < nblocks ? row[i] : 0u;
+        unsigned x = v; // inclusive warp scan
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) wsum[warp] = x;
         __syncthreads();
-        part[threadIdx.x] += v;
+        if (warp == 0) {
+            unsigned w = wsum[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned y = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += y;
+            }
+            wsum[lane] = w; // inclusive over warps
+        }
+        __syncthreads();
+        const unsigned before = carry + (warp ? wsum[warp - 1] : 0u);
+        if (i < nblocks) row[i] = before + x - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = before + x;
         __syncthreads();
     }
-    unsigned run = part[threadIdx.x] - s; // exclusive base of this chunk
-    for (unsigned i = b; i < e; ++i) {
-        const unsigned v = a[i];
-        a[i] = run;
-        run += v;
-    }
+    if (threadIdx.x == 0) totals[blockIdx.x] = carry;
 }
 
 __global__ void __launch_bounds__(SORT_THREADS)
     scatter(const uint64_t *__restrict__ kin, const unsigned *__restrict__ vin,
             uint64_t *__restrict__ kout, unsigned *__restrict__ vout, unsigned n, int shift,
-            unsigned nblocks, const unsigned *__restrict__ base)
+            unsigned nblocks, const unsigned *__restrict__ base,
+            const unsigned *__restrict__ totals)
 {
     __shared__ unsigned wcount[SORT_WARPS][256];
+    __shared__ unsigned dbase[256]; // keys with a smaller digit, all tiles
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
     for (int i = threadIdx.x; i < SORT_WARPS * 256; i += SORT_THREADS) (&wcount[0][0])[i] = 0;
+    { // exclusive scan of the 256 digit totals (8 warps x 32 digits)
+        const unsigned t = totals[threadIdx.x];
+        unsigned x = t;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        dbase[threadIdx.x] = x - t; // exclusive inside the warp's 32 digits
+        __syncthreads();
+        unsigned before = 0;
+        for (int w = 0; w < warp; ++w) before += dbase[w * 32 + 31] + totals[w * 32 + 31];
+        __syncthreads();
+        dbase[threadIdx.x] = before + x - t;
+    }
     __syncthreads();
 
     uint64_t key[SORT_ITEMS];
@@ -100,7 +133,7 @@ __global__ void __launch_bounds__(SORT_THREADS)
     __syncthreads();
     { // digit t: running offsets over the CTA's warps + the global base of (digit, tile)
         const unsigned t = threadIdx.x;
-        unsigned run = base[(size_t)t * nblocks + blockIdx.x];
+        unsigned run = dbase[t] + base[(size_t)t * nblocks + blockIdx.x];
 #pragma unroll
         for (int w = 0; w < SORT_WARPS; ++w) {
             const unsigned c = wcount[w][t];
@@ -134,9 +167,9 @@ cudaError_t bh_radix_sort(BhTree *t, unsigned n, int bits, cudaStream_t s, unsig
     for (int p = 0; p < passes; ++p) {
         const int in = p & 1, out = in ^ 1, shift = 8 * p;
         digit_histogram<<<nb, SORT_THREADS, 0, s>>>(t->key[in], n, shift, nb, t->hist);
-        exclusive_scan<<<1, 1024, 0, s>>>(t->hist, 256u * nb);
+        scan_rows<<<256, 1024, 0, s>>>(t->hist, nb, t->hist + (size_t)256 * nb);
         scatter<<<nb, SORT_THREADS, 0, s>>>(t->key[in], t->val[in], t->key[out], t->val[out], n,
-                                            shift, nb, t->hist);
+                                            shift, nb, t->hist, t->hist + (size_t)256 * nb);
         if (launches) *launches += 3;
     }
     return cudaGetLastError();
