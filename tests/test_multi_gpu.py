@@ -151,3 +151,26 @@ def test_overlap_and_serial_exchange_agree(nb):
                   tune_flags=nb.TUNE_NO_OVERLAP)
     assert a[0][2] == 3 and b[0][2] == 0
     assert rel_err(a[0][0], b[0][0]).max() <= 1e-11 and rel_err(a[0][1], b[0][1]).max() <= 1e-11
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_barnes_hut_ranks_bitwise(nb, world):
+    """Barnes-Hut over W ranks: every rank builds the same tree from the gathered positions and
+    walks the bodies of its own slice; a body's interaction list does not depend on who walks
+    it, so the W-rank state equals the 1-rank state bit for bit."""
+    need(nb, world)
+    g = golden("10k_bodies_g1")
+    kw = dict(precision=nb.PREC_FP64, algorithm=nb.ALGO_BARNES_HUT, dt=g["dt"])
+    with nb.Engine(g["pos_xyzm"], g["vel"], **kw) as e:
+        a1 = e.accelerations()
+        e.step(3)
+        p1, v1 = e.gather()
+
+    def fn(e, r):
+        acc = e.accelerations()
+        e.step(3)
+        p, v = e.gather()
+        return acc, p, v
+
+    for acc, p, v in run_ranks(nb, world, fn, g["pos_xyzm"], g["vel"], **kw):
+        assert np.array_equal(acc, a1) and np.array_equal(p, p1) and np.array_equal(v, v1)
