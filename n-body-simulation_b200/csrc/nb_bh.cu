@@ -220,7 +220,11 @@ __global__ void __launch_bounds__(BH_THREADS)
 // drops out of its subtree.  Each body therefore sees exactly the serial
 // reference's interaction list, in the reference's order (children 0..7,
 // depth first), and agrees with it to rounding, not just within the THETA
-// envelope.
+// envelope.  An opened cell's eight children are fetched by eight lanes at once
+// and tested in one go (one memory round trip per OPENED cell instead of one per
+// visited node); only cells that some lane must open go through the stack.  The
+// sum order therefore is "a cell's accepted children first, then its opened
+// children's subtrees" -- the reference's terms, regrouped.
 //
 // Acceptance is tested as border^2 < THETA^2 * dist^2 -- the reference's
 // border / dist < THETA (:405) without the FP64 divide and square root; the two
@@ -253,10 +257,20 @@ __device__ __forceinline__ double bh_inv_r3_times_m(double r2, double m)
     return fma(u, q, u);
 }
 
+// One child of an opened node as the warp sees it: staged in shared memory by
+// the lane that fetched it, then read by all lanes as a broadcast.
+struct __align__(16) ChildSlot {
+    double4 c;  // body: x,y,z,m; cell: centre of mass + mass
+    double b2;  // cell: border^2 at its depth; body: -1 (always "far enough")
+    int ent;    // >= 0 body (sorted index), <= -2 cell -(id + 2)
+    int pad;
+};
+
+template <bool COUNT>
 __global__ void __launch_bounds__(TRAV_WARPS * 32) traverse_kernel(const TravArgs a)
 {
-    __shared__ int s_ent[TRAV_WARPS][TRAV_STACK];
-    __shared__ unsigned s_mask[TRAV_WARPS][TRAV_STACK];
+    __shared__ uint2 s_stack[TRAV_WARPS][TRAV_STACK]; // {cell id | depth << 27, lanes that must open it}
+    __shared__ ChildSlot s_child[TRAV_WARPS][8];
     __shared__ double s_border2[BH_MAX_LEVEL + 2];
     if (threadIdx.x <= BH_MAX_LEVEL) {
         double b = 2.0 * a.bbox[0]; // root border = max (serial/barnes-hut.c:470), halved per level
@@ -265,88 +279,107 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32) traverse_kernel(const TravArg
     }
     __syncthreads();
 
+    // pointers and scalars in registers: the walk below is issue-bound, not FP64-bound
+    const double4 *__restrict__ spos = a.spos;
+    const double4 *__restrict__ com = a.com;
+    const int *__restrict__ child = a.child;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned lt = (1u << lane) - 1u;
     const unsigned n_own = a.own ? a.flags[2] : a.n_own_static;
     const unsigned j = (blockIdx.x * TRAV_WARPS + warp) * 32 + lane;
     const bool valid = j < n_own;
     const unsigned k = valid ? (a.own ? a.own[j] : j) : 0u;
-    const double4 me = a.spos[k];
+    const double4 me = spos[k];
     const double theta2 = a.p.theta * a.p.theta, eps2 = a.p.eps2;
     double ax = 0, ay = 0, az = 0;
     unsigned n_inter = 0, n_visit = 0;
-    int *ent = s_ent[warp];
-    unsigned *msk = s_mask[warp];
+    uint2 *stk = s_stack[warp];
+    ChildSlot *slot = s_child[warp];
     int sp = 0;
     const unsigned all = __ballot_sync(0xffffffffu, valid);
-    if (all && a.p.n >= 2) { // a single body feels nothing (root needs >= 2 bodies)
-        if (lane == 0) { ent[0] = -2; msk[0] = all; }
-        sp = 1;
-    }
-    __syncwarp();
-    while (sp > 0) {
-        --sp;
-        const int e = ent[sp];
-        const unsigned M = msk[sp];
-        __syncwarp();
-        const bool in = (M >> lane) & 1u;
-        if (e >= 0) { // a body (leaf): calculate_acceleration, skipping the body itself (:411)
-            if (in && (unsigned)e != k) {
-                const double4 b = a.spos[e];
-                const double dx = b.x - me.x, dy = b.y - me.y, dz = b.z - me.z;
-                const double r2 = fma(dz, dz, fma(dy, dy, fma(dx, dx, eps2)));
-                const double s = bh_inv_r3_times_m(r2, b.w);
-                ax = fma(dx, s, ax); ay = fma(dy, s, ay); az = fma(dz, s, az);
-                ++n_inter; ++n_visit;
-            }
-            continue;
-        }
-        const unsigned nd = (unsigned)(-e - 2);
-        const double4 c = a.com[nd];
-        const unsigned lvl = a.level[nd];
+
+    // One candidate (a body or a cell) against the warp's 32 bodies, for the lanes in M.
+    // A lane takes it if it is far enough (border^2 < THETA^2 dist^2; bodies carry border^2 = -1)
+    // and it is not the lane's own body (:411).  Returns the lanes that took it; for a cell the
+    // others of M must open it.  Branch-free per lane: a lane that does not take the
+    // interaction multiplies by a zero mass.
+    auto consider = [&](const double4 &c, double b2, int ent, unsigned M) -> unsigned {
         const double dx = c.x - me.x, dy = c.y - me.y, dz = c.z - me.z;
         // |d|^2 with FMAs: 1 ulp off the reference's mul/add form (:101-104), which moves an
         // accept/open decision only if border/dist sits within an ulp of THETA
         const double d2 = fma(dz, dz, fma(dy, dy, dx * dx));
-        const bool accept = in && (s_border2[lvl] < theta2 * d2);
-        if (in) ++n_visit;
-        if (accept) {
-            const double s = bh_inv_r3_times_m(d2 + eps2, c.w);
+        const bool take = ((M >> lane) & 1u) && (b2 < theta2 * d2) && (ent != (int)k);
+        const unsigned T = __ballot_sync(0xffffffffu, take);
+        if (T) {
+            const double s = bh_inv_r3_times_m(d2 + eps2, take ? c.w : 0.0);
             ax = fma(dx, s, ax); ay = fma(dy, s, ay); az = fma(dz, s, az);
-            ++n_inter;
         }
-        const unsigned O = __ballot_sync(0xffffffffu, in && !accept);
-        if (!O) continue;
+        if (COUNT) {
+            n_inter += take;
+            n_visit += ent >= 0 ? take : (M >> lane) & 1u; // the body's own leaf is never visited
+        }
+        return T;
+    };
+
+    if (all && a.p.n >= 2) { // a single body feels nothing (the root needs >= 2 bodies)
+        // the root is tested like any cell (:405)
+        const unsigned O = all & ~consider(com[0], s_border2[0], -2, all);
+        if (O) {
+            if (lane == 0) stk[0] = make_uint2(0u, O); // id 0, depth 0
+            sp = 1;
+        }
+    }
+    __syncwarp();
+    while (sp > 0) {
+        --sp;
+        const uint2 top = stk[sp];
+        const unsigned nd = top.x & 0x07ffffffu, lvl = top.x >> 27, M = top.y;
         if (lvl == BH_MAX_LEVEL) { // bucket: bodies sharing one finest cell, summed directly
             const unsigned f = a.first[nd], cn = a.count[nd];
             for (unsigned t = f; t < f + cn; ++t) {
-                if (((O >> lane) & 1u) && t != k) {
-                    const double4 b = a.spos[t];
-                    const double bx = b.x - me.x, by = b.y - me.y, bz = b.z - me.z;
-                    const double r2 = fma(bz, bz, fma(by, by, fma(bx, bx, eps2)));
-                    const double s = bh_inv_r3_times_m(r2, b.w);
-                    ax = fma(bx, s, ax); ay = fma(by, s, ay); az = fma(bz, s, az);
-                    ++n_inter;
-                }
+                consider(spos[t], -1.0, (int)t, M);
+                if (COUNT) n_visit -= (M >> lane) & 1u && t != k; // members are not tree nodes
             }
             continue;
         }
-        const int ch = lane < 8 ? a.child[(size_t)nd * 8 + lane] : -1;
+        // lanes 0..7 fetch the eight children (id, then COM or body) and stage the ones that
+        // exist, packed in octant order
+        int ch = -1;
+        if (lane < 8) ch = child[(size_t)nd * 8 + lane];
         const unsigned vb = __ballot_sync(0xffffffffu, ch != -1);
-        const int nv = __popc(vb);
-        if (sp + nv > TRAV_STACK) { // cannot happen for depth <= BH_MAX_LEVEL; flagged, not silent
+        const int nc = __popc(vb), my = __popc(vb & lt);
+        if (ch != -1) {
+            ChildSlot cs;
+            cs.ent = ch;
+            cs.pad = 0;
+            if (ch >= 0) { cs.c = spos[ch]; cs.b2 = -1.0; }
+            else { cs.c = com[-ch - 2]; cs.b2 = s_border2[lvl + 1]; }
+            slot[my] = cs;
+        }
+        __syncwarp();
+        // the cells some lane must open go to the stack, reversed so that the first child is
+        // walked first (the reference's depth-first order)
+        unsigned pend = 0, mine = 0; // slots to push; the lane that staged a slot keeps its mask
+        for (int c = 0; c < nc; ++c) {
+            const ChildSlot cs = slot[c];
+            const unsigned T = consider(cs.c, cs.b2, cs.ent, M);
+            const unsigned O = cs.ent < 0 ? (M & ~T) : 0u;
+            if (my == c) mine = O;
+            if (O) pend |= 1u << c;
+        }
+        const int np = __popc(pend);
+        if (sp + np > TRAV_STACK) { // cannot happen for depth <= BH_MAX_LEVEL; flagged, not silent
             if (lane == 0) a.flags[1] = 1;
             break;
         }
-        if (ch != -1) { // reversed, so that child 0 is popped first
-            const int r = __popc(vb & ((1u << lane) - 1u));
-            ent[sp + nv - 1 - r] = ch;
-            msk[sp + nv - 1 - r] = O;
-        }
-        sp += nv;
+        if (ch != -1 && mine)
+            stk[sp + np - 1 - __popc(pend & ((1u << my) - 1u))] =
+                make_uint2((unsigned)(-ch - 2) | ((lvl + 1u) << 27), mine);
+        sp += np;
         __syncwarp();
     }
 
-    if (a.p.count_visits && a.counters) {
+    if (COUNT && a.counters) {
         unsigned long long ni = n_inter, nv = n_visit;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -400,7 +433,7 @@ __global__ void reset_kernel(unsigned *level_count, unsigned *flags, double *bbo
 } // namespace
 
 // ------------------------------------------------------------------ host ----
-static unsigned bh_node_cap(unsigned n) { return 2u * n + 4096u; }
+static unsigned bh_node_cap(unsigned n) { return 2u * n + 4096u; } // < 2^27: ids share a word with the depth
 
 size_t bh_bytes(unsigned n)
 {
@@ -494,7 +527,8 @@ cudaError_t bh_evaluate(BhTree *t, const BhParams &p, cudaStream_t s, unsigned *
     const unsigned max_own = sliced ? (p.own_end > p.own_begin ? min(p.own_end, n) - min(p.own_begin, n) : 0u) : n;
     if (max_own) {
         const unsigned tgrid = (max_own + TRAV_WARPS * 32 - 1) / (TRAV_WARPS * 32);
-        traverse_kernel<<<tgrid, TRAV_WARPS * 32, 0, s>>>(ta);
+        if (p.count_visits) traverse_kernel<true><<<tgrid, TRAV_WARPS * 32, 0, s>>>(ta);
+        else traverse_kernel<false><<<tgrid, TRAV_WARPS * 32, 0, s>>>(ta);
         ++nl;
     }
     if (launches) *launches += nl;

@@ -436,9 +436,11 @@ cudaError_t plan_direct_f32(DirectPlan *plan, const SliceGeom &sg, int sm_count,
 {
     const unsigned slice_units = sg.slice_units, n_units = sg.n_units;
     const unsigned slice_bodies = slice_units * 4u;
-    int v = 0;
-    if (slice_bodies < 16384u) v = 2;
-    else if (slice_bodies < 148u * 2048u) v = 1;
+    // size class by work (i x j), not by slice length: a rank of an 8-GPU run owns 125k of 1M
+    // bodies and still wants the large class.  Measured on B200 (tools/probe_perf.py): large wins
+    // from 50k^2 up (2.42e12/s vs 2.32 medium, 2.23 small), small below 20k^2 (2.03 vs 1.93).
+    const double work = (double)slice_bodies * (double)n_units * 4.0;
+    int v = work >= 9.0e8 ? 0 : 2;
     const int forced = (tune_flags >> 8) & 0xf;
     if (forced >= 1 && forced <= kNumVariants) v = forced - 1;
     const VariantF32 &k = kVariants[v];
