@@ -110,6 +110,9 @@ struct BuildArgs {
     unsigned *level_count;
     unsigned *flags;
     unsigned node_cap;
+    const double4 *spos;
+    ChildRec *cblock;
+    unsigned *pslot;
 };
 
 __device__ __forceinline__ unsigned level_base(const unsigned *level_count, int L)
@@ -169,6 +172,22 @@ __global__ void __launch_bounds__(BH_THREADS) build_level_kernel(BuildArgs a, in
             }
         }
         a.child[(size_t)nd * 8 + oct] = ch;
+        // the traversal's view: non-empty children packed to the front of the node's block
+        const unsigned nonempty = (__ballot_sync(gmask, k != 0) >> ((threadIdx.x & 31) & ~7)) & 0xffu;
+        const unsigned at = nd * 8u + (unsigned)__popc(nonempty & ((1u << oct) - 1u));
+        if (k == 1) {
+            ChildRec r;
+            r.c = a.spos[start];
+            r.b2 = -1.0;
+            r.ent = (int)start;
+            a.cblock[at] = r;
+        } else if (ch <= -2) {
+            a.cblock[at].ent = ch;           // centre of mass and border^2 follow in com_level_kernel
+            a.pslot[-ch - 2] = at;
+        } else if (k >= 2) {
+            a.cblock[at].ent = -1;           // node pool exhausted: the list ends here (flagged)
+        }
+        if (oct == 7 && __popc(nonempty) < 8) a.cblock[nd * 8u + __popc(nonempty)].ent = -1;
     }
 }
 
@@ -181,8 +200,13 @@ __global__ void __launch_bounds__(BH_THREADS)
     com_level_kernel(const double4 *__restrict__ spos, const int *__restrict__ child,
                      const unsigned *__restrict__ first, const unsigned *__restrict__ count,
                      const unsigned *__restrict__ level_count, double4 *__restrict__ com, int L,
-                     unsigned node_cap)
+                     unsigned node_cap, const double *__restrict__ bbox,
+                     ChildRec *__restrict__ cblock, const unsigned *__restrict__ pslot)
 {
+    // border^2 at depth L: (max / 2^L)^2, the halvings are exact
+    double border = 2.0 * bbox[0];
+    for (int l = 0; l < L; ++l) border /= 2;
+    const double b2 = border * border;
     const unsigned base = level_base(level_count, L);
     const unsigned cnt = level_nodes(level_count, L, base, node_cap);
     for (unsigned g = blockIdx.x * blockDim.x + threadIdx.x; g < cnt; g += gridDim.x * blockDim.x) {
@@ -207,6 +231,11 @@ __global__ void __launch_bounds__(BH_THREADS)
             }
         }
         com[nd] = make_double4(cx, cy, cz, cm);
+        if (L > 0) {
+            ChildRec *r = &cblock[pslot[nd]];
+            r->c = make_double4(cx, cy, cz, cm);
+            r->b2 = b2;
+        }
     }
 }
 
@@ -234,7 +263,7 @@ constexpr int TRAV_STACK = 7 * (BH_MAX_LEVEL + 1) + 16; // <= 7 siblings pending
 
 struct TravArgs {
     const double4 *spos, *com;
-    const int *child;
+    const ChildRec *cblock;
     const unsigned *first, *count, *perm, *own;
     const unsigned char *level;
     const double *bbox;
@@ -257,20 +286,11 @@ __device__ __forceinline__ double bh_inv_r3_times_m(double r2, double m)
     return fma(u, q, u);
 }
 
-// One child of an opened node as the warp sees it: staged in shared memory by
-// the lane that fetched it, then read by all lanes as a broadcast.
-struct __align__(16) ChildSlot {
-    double4 c;  // body: x,y,z,m; cell: centre of mass + mass
-    double b2;  // cell: border^2 at its depth; body: -1 (always "far enough")
-    int ent;    // >= 0 body (sorted index), <= -2 cell -(id + 2)
-    int pad;
-};
-
 template <bool COUNT>
 __global__ void __launch_bounds__(TRAV_WARPS * 32) traverse_kernel(const TravArgs a)
 {
     __shared__ uint2 s_stack[TRAV_WARPS][TRAV_STACK]; // {cell id | depth << 27, lanes that must open it}
-    __shared__ ChildSlot s_child[TRAV_WARPS][8];
+    __shared__ ChildRec s_child[TRAV_WARPS][8];
     __shared__ double s_border2[BH_MAX_LEVEL + 2];
     if (threadIdx.x <= BH_MAX_LEVEL) {
         double b = 2.0 * a.bbox[0]; // root border = max (serial/barnes-hut.c:470), halved per level
@@ -282,9 +302,8 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32) traverse_kernel(const TravArg
     // pointers and scalars in registers: the walk below is issue-bound, not FP64-bound
     const double4 *__restrict__ spos = a.spos;
     const double4 *__restrict__ com = a.com;
-    const int *__restrict__ child = a.child;
+    const ChildRec *__restrict__ cblock = a.cblock;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const unsigned lt = (1u << lane) - 1u;
     const unsigned n_own = a.own ? a.flags[2] : a.n_own_static;
     const unsigned j = (blockIdx.x * TRAV_WARPS + warp) * 32 + lane;
     const bool valid = j < n_own;
@@ -294,7 +313,7 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32) traverse_kernel(const TravArg
     double ax = 0, ay = 0, az = 0;
     unsigned n_inter = 0, n_visit = 0;
     uint2 *stk = s_stack[warp];
-    ChildSlot *slot = s_child[warp];
+    ChildRec *slot = s_child[warp];
     int sp = 0;
     const unsigned all = __ballot_sync(0xffffffffu, valid);
 
@@ -342,40 +361,39 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32) traverse_kernel(const TravArg
             }
             continue;
         }
-        // lanes 0..7 fetch the eight children (id, then COM or body) and stage the ones that
-        // exist, packed in octant order
-        int ch = -1;
-        if (lane < 8) ch = child[(size_t)nd * 8 + lane];
-        const unsigned vb = __ballot_sync(0xffffffffu, ch != -1);
-        const int nc = __popc(vb), my = __popc(vb & lt);
-        if (ch != -1) {
-            ChildSlot cs;
-            cs.ent = ch;
-            cs.pad = 0;
-            if (ch >= 0) { cs.c = spos[ch]; cs.b2 = -1.0; }
-            else { cs.c = com[-ch - 2]; cs.b2 = s_border2[lvl + 1]; }
-            slot[my] = cs;
+        // The node's child records are one 512-byte block: lanes 0..7 fetch one record each
+        // (one coalesced round trip per opened cell) and stage them in shared memory, from
+        // where all lanes read them as broadcasts.  Cells that some lane must open go to the
+        // stack; walking the list backwards leaves the first child on top, so it is walked
+        // first (the reference's depth-first order).
+        const ChildRec *blk = cblock + (size_t)nd * 8;
+        int ent_l = 0;
+        if (lane < 8) {
+            const double4 cc = blk[lane].c;
+            const double2 be = *reinterpret_cast<const double2 *>(&blk[lane].b2); // b2 | ent, pad
+            slot[lane].c = cc;
+            *reinterpret_cast<double2 *>(&slot[lane].b2) = be;
+            ent_l = __double2loint(be.y);
         }
-        __syncwarp();
-        // the cells some lane must open go to the stack, reversed so that the first child is
-        // walked first (the reference's depth-first order)
-        unsigned pend = 0, mine = 0; // slots to push; the lane that staged a slot keeps its mask
-        for (int c = 0; c < nc; ++c) {
-            const ChildSlot cs = slot[c];
-            const unsigned T = consider(cs.c, cs.b2, cs.ent, M);
-            const unsigned O = cs.ent < 0 ? (M & ~T) : 0u;
-            if (my == c) mine = O;
-            if (O) pend |= 1u << c;
-        }
-        const int np = __popc(pend);
-        if (sp + np > TRAV_STACK) { // cannot happen for depth <= BH_MAX_LEVEL; flagged, not silent
+        // the list ends at the first record with ent == -1 (what follows it is stale)
+        const unsigned endm = __ballot_sync(0xffffffffu, ent_l == -1);
+        const int nc = endm ? __ffs(endm) - 1 : 8;
+        if (sp + nc > TRAV_STACK) { // cannot happen for depth <= BH_MAX_LEVEL; flagged, not silent
             if (lane == 0) a.flags[1] = 1;
             break;
         }
-        if (ch != -1 && mine)
-            stk[sp + np - 1 - __popc(pend & ((1u << my) - 1u))] =
-                make_uint2((unsigned)(-ch - 2) | ((lvl + 1u) << 27), mine);
-        sp += np;
+        __syncwarp();
+        for (int c = nc - 1; c >= 0; --c) {
+            const double4 cc = slot[c].c;
+            const double b2 = slot[c].b2;
+            const int ent = slot[c].ent;
+            const unsigned T = consider(cc, b2, ent, M);
+            const unsigned O = ent < 0 ? (M & ~T) : 0u;
+            if (O) {
+                if (lane == 0) stk[sp] = make_uint2((unsigned)(-ent - 2) | ((lvl + 1u) << 27), O);
+                ++sp;
+            }
+        }
         __syncwarp();
     }
 
@@ -438,7 +456,7 @@ static unsigned bh_node_cap(unsigned n) { return 2u * n + 4096u; } // < 2^27: id
 size_t bh_bytes(unsigned n)
 {
     const size_t cap = bh_node_cap(n), nn = n ? n : 1;
-    return nn * (2 * 8 + 2 * 4 + 32 + 4) + cap * (32 + 32 + 4 + 4 + 1) +
+    return nn * (2 * 8 + 2 * 4 + 32 + 4) + cap * (32 + 32 + 4 + 4 + 1 + 512 + 4) +
            (size_t)256 * bh_sort_blocks(n) * 4 + 4096;
 }
 
@@ -465,6 +483,8 @@ cudaError_t bh_alloc(BhTree *t, unsigned n)
     BH_TRY(cudaMalloc(&t->first, (size_t)t->node_cap * sizeof(unsigned)));
     BH_TRY(cudaMalloc(&t->count, (size_t)t->node_cap * sizeof(unsigned)));
     BH_TRY(cudaMalloc(&t->level, (size_t)t->node_cap));
+    BH_TRY(cudaMalloc(&t->cblock, (size_t)t->node_cap * 8 * sizeof(ChildRec)));
+    BH_TRY(cudaMalloc(&t->pslot, (size_t)t->node_cap * sizeof(unsigned)));
     BH_TRY(cudaMalloc(&t->level_count, (BH_MAX_LEVEL + 2) * sizeof(unsigned)));
     BH_TRY(cudaMalloc(&t->flags, 4 * sizeof(unsigned)));
     BH_TRY(cudaMemset(t->flags, 0, 4 * sizeof(unsigned)));
@@ -478,7 +498,7 @@ cudaError_t bh_alloc(BhTree *t, unsigned n)
 void bh_free(BhTree *t)
 {
     void *bufs[] = {t->key[0], t->key[1], t->val[0], t->val[1], t->spos, t->own, t->com, t->child,
-                    t->first, t->count, t->level, t->level_count, t->flags, t->bbox, t->hist,
+                    t->first, t->count, t->level, t->cblock, t->pslot, t->level_count, t->flags, t->bbox, t->hist,
                     t->counters};
     for (void *b : bufs)
         if (b) cudaFree(b);
@@ -507,18 +527,19 @@ cudaError_t bh_evaluate(BhTree *t, const BhParams &p, cudaStream_t s, unsigned *
     }
     if (n >= 2) {
         BuildArgs ba{t->key[0], t->first, t->count, t->level, t->child, t->level_count, t->flags,
-                     t->node_cap};
+                     t->node_cap, t->spos, t->cblock, t->pslot};
         // a level holds at most n/2 nodes, 8 lanes each
         const unsigned bgrid = min(wide, (n / 2 * 8 + BH_THREADS - 1) / BH_THREADS + 1);
         for (int L = 0; L < BH_MAX_LEVEL; ++L) build_level_kernel<<<bgrid, BH_THREADS, 0, s>>>(ba, L);
         const unsigned cgrid = min(wide, (n / 2 + BH_THREADS - 1) / BH_THREADS + 1);
         for (int L = BH_MAX_LEVEL; L >= 0; --L)
             com_level_kernel<<<cgrid, BH_THREADS, 0, s>>>(t->spos, t->child, t->first, t->count,
-                                                          t->level_count, t->com, L, t->node_cap);
+                                                          t->level_count, t->com, L, t->node_cap, t->bbox,
+                                                          t->cblock, t->pslot);
         nl += 2 * BH_MAX_LEVEL + 1;
     }
     TravArgs ta;
-    ta.spos = t->spos; ta.com = t->com; ta.child = t->child;
+    ta.spos = t->spos; ta.com = t->com; ta.cblock = t->cblock;
     ta.first = t->first; ta.count = t->count; ta.perm = t->val[0];
     ta.own = sliced ? t->own : nullptr;
     ta.level = t->level; ta.bbox = t->bbox; ta.flags = t->flags; ta.counters = t->counters;

@@ -20,6 +20,14 @@ constexpr int BH_MAX_LEVEL = 21; // 3 x 21 = 63 key bits; deeper cells become bu
 // Device buffers of one engine's tree.  Bodies are referred to by their rank k
 // in Morton order ("sorted index"); perm[k] is the body's index in the state
 // arrays.
+// A child as the traversal sees it (64 bytes, 2 per 128-byte line).
+struct __align__(32) ChildRec {
+    double4 c;  // body: x,y,z,m; cell: centre of mass + mass
+    double b2;  // cell: border^2 at its depth; body: -1 (always "far enough")
+    int ent;    // >= 0 body (sorted index), <= -2 cell -(id + 2), -1 end of list
+    int pad[5];
+};
+
 struct BhTree {
     unsigned n = 0;        // real bodies
     unsigned node_cap = 0; // internal-node pool size
@@ -33,6 +41,11 @@ struct BhTree {
     int *child = nullptr;     // [node][8]: -1 empty, >= 0 body (sorted index), <= -2 node -(c+2)
     unsigned *first = nullptr, *count = nullptr; // the node's bodies: sorted range
     unsigned char *level = nullptr;              // depth (root = 0)
+    // what the traversal reads: per node one 512-byte block of up to 8 child records
+    // (non-empty children packed to the front, octant order kept), each carrying
+    // everything the walk needs about the child -- so opening a cell is ONE round trip
+    struct ChildRec *cblock = nullptr; // [node][8]
+    unsigned *pslot = nullptr;         // node -> index of its record in the parent's block
     // bookkeeping (device)
     unsigned *level_count = nullptr; // [BH_MAX_LEVEL + 2] nodes per level
     unsigned *flags = nullptr;       // [0] node-pool overflow, [1] stack overflow, [2] own count
