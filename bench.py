@@ -342,6 +342,144 @@ def run_gpu_arm(args):
         dist.destroy_process_group()
 
 
+# ------------------------------------------------------- Barnes-Hut arm ----
+def bh_cpu_baseline(pm, vel, sample_n, threads):
+    """The reference's barnes-hut-omp (openmp/barnes-hut.c, -O3, compiled in place into
+    oracle/_ref) on the first sample_n bodies, one step = two force evaluations; timed by its
+    own 'Elapsed wall time' line (the CSV read is outside it, as in the reference)."""
+    import re
+    import tempfile
+    import oracle as O
+    from conftest import load_package
+    exe = os.path.join(O.REFDIR, "barnes_hut_omp_fast")
+    if not os.path.exists(exe):
+        return None
+    h = load_package().load_host_library()
+    with tempfile.TemporaryDirectory() as td:
+        inp = os.path.join(td, "in.csv")
+        h.nbh_write_bodies(inp.encode(), sample_n, np.ascontiguousarray(pm[:sample_n]),
+                           np.ascontiguousarray(vel[:sample_n]))
+        r = subprocess.run([exe, inp, "0", "0.01", "0.01", os.path.join(td, "o.csv"), str(threads)],
+                           capture_output=True, text=True, timeout=600)
+    m = re.search(r"Elapsed wall time: ([0-9.]+)", r.stdout)
+    if not m:
+        return None
+    sec = float(m.group(1))
+    return {"value": 2.0 * sample_n / sec, "unit": "body force evaluations/s", "cores": threads,
+            "kind": "reference",
+            "sample": "barnes-hut-omp (openmp/barnes-hut.c, -O3) on the first %d bodies, 1 step "
+                      "(2 evaluations), %.2f s by its own clock" % (sample_n, sec)}
+
+
+def run_bh_arm(args):
+    """BASELINE configs 4/5: Barnes-Hut (THETA = 0.5, FP64) on a Plummer sphere; value = body
+    force evaluations per second (bodies x steps / time), accuracy against the direct-sum
+    kernel on the same positions when that is affordable (<= 2M bodies, 1 GPU)."""
+    import torch
+    from conftest import load_package, rel_err
+    nb = load_package()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist, comm = None, None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        comm = nb.share_comm_id(dist, rank, device="cuda")
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    n = args.bodies
+    pm, vel = plummer(n)
+    eng = nb.Engine(pm, vel, precision=nb.PREC_FP64, algorithm=nb.ALGO_BARNES_HUT, device=local,
+                    rank=rank, world=world, comm_id_bytes=comm, tune_flags=nb.TUNE_COUNT_VISITS)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    for _ in range(args.warmup):
+        eng.step(1)
+    eng.sync()
+    l0 = eng.stats().kernel_launches
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    dev_ms = 0.0
+    for _ in range(args.steps):
+        flush.zero_()
+        torch.cuda.synchronize()
+        eng.step(1)
+        dev_ms += eng.stats().last_step_ms
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    launches = eng.stats().kernel_launches - l0
+    ti = eng.tree_stats()
+    t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms = float(t[0])
+    # end to end through the C ABI: upload, one step, gather (2 evaluations)
+    hp, hv = torch.from_numpy(pm).pin_memory(), torch.from_numpy(vel).pin_memory()
+    op, ov = torch.empty_like(hp).pin_memory(), torch.empty_like(hv).pin_memory()
+
+    def e2e_once():
+        eng.upload_raw(hp.data_ptr(), hv.data_ptr())
+        eng.step(1)
+        eng.gather_raw(op.data_ptr(), ov.data_ptr())
+
+    e2e_once()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        e2e_once()
+    barrier()
+    tw = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(tw, op=dist.ReduceOp.MAX)
+    e2e_value = 3 * 2.0 * n / float(tw[0])
+    acc_stats = None
+    if world == 1 and n <= 2_000_000 and not args.no_accuracy:
+        eng.upload(pm, vel)
+        a_bh = eng.accelerations()
+        with nb.Engine(pm, vel, precision=nb.PREC_FP64, device=local) as d:
+            a_dir = d.accelerations()
+        err = rel_err(a_bh, a_dir)
+        acc_stats = {"median": float(np.median(err)), "p99": float(np.percentile(err, 99)),
+                     "max": float(err.max()),
+                     "what": "per-body relative acceleration error vs the FP64 direct-sum kernel"}
+    if rank == 0:
+        my = n / world
+        line = {
+            "metric": "Barnes-Hut body force evaluations/s", "value": n * args.steps / (dev_ms * 1e-3),
+            "unit": "bodies/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "synthetic %d-body Plummer sphere, Barnes-Hut THETA=0.5, fp64, "
+                                   "i-slices over %d GPU(s), tree replicated" % (n, world),
+                       "bodies": n, "theta": 0.5, "generator": "plummer seed 17",
+                       "l2": "flushed between timed steps (256 MiB write)"},
+            "clocks": clocks,
+            "tree": {"nodes": ti.nodes, "depth": ti.depth,
+                     "interactions_per_body": ti.interactions / my, "visits_per_body": ti.node_visits / my},
+            "accuracy_vs_direct": acc_stats,
+            "e2e": {"value": e2e_value, "unit": "bodies/s", "h2d_bytes_per_step": int(hp.numel() * 8 + hv.numel() * 8),
+                    "d2h_bytes_per_step": int(op.numel() * 8 + ov.numel() * 8),
+                    "what": "nb_upload + nb_step(1) + nb_gather per step = 2 evaluations"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": None, "peak": None, "unit": "GB/s", "frac": None,
+                         "traffic": None, "note": "latency/issue-bound tree walk, see DESIGN.md 4.3"},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = bh_cpu_baseline(pm, vel, min(n, 200_000), os.cpu_count() or 1)
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -355,8 +493,13 @@ def main():
     ap.add_argument("--ctas-per-sm", type=int, default=0)
     ap.add_argument("--tune-flags", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--algorithm", default="direct", choices=["direct", "bh"],
+                    help="direct = the headline exhaustive FP32 step; bh = Barnes-Hut (configs 4/5)")
+    ap.add_argument("--no-accuracy", action="store_true")
     args = ap.parse_args()
-    if args.impl == "reference":
+    if args.algorithm == "bh" and args.impl != "reference":
+        run_bh_arm(args)
+    elif args.impl == "reference":
         run_reference_arm(args)
     else:
         run_gpu_arm(args)

@@ -68,31 +68,49 @@ __global__ void __launch_bounds__(BH_THREADS)
 }
 
 // Order-preserving compaction of the sorted indices whose body lies in
-// [own_begin, own_end): one CTA pass with a running base (n / 256 iterations of
-// a 256-wide ballot scan; O(n) work, used only when the slice is not everything).
-__global__ void __launch_bounds__(1024)
-    own_list_kernel(const unsigned *__restrict__ perm, unsigned n, unsigned own_begin,
-                    unsigned own_end, unsigned *__restrict__ own, unsigned *__restrict__ n_own)
+// [own_begin, own_end) (multi-rank runs: the bodies this rank integrates, in
+// Morton order): per-tile counts, an exclusive scan of the counts
+// (bh_exclusive_scan), then every tile writes its members behind its base.
+constexpr int OWN_TILE = 1024;
+
+__device__ __forceinline__ unsigned own_rank_in_tile(bool mine, unsigned *wsum, unsigned *total)
 {
-    __shared__ unsigned wsum[32];
-    __shared__ unsigned base;
-    if (threadIdx.x == 0) base = 0;
-    __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (unsigned k0 = 0; k0 < n; k0 += 1024) {
-        const unsigned k = k0 + threadIdx.x;
-        const bool mine = k < n && perm[k] >= own_begin && perm[k] < own_end;
-        const unsigned bal = __ballot_sync(0xffffffffu, mine);
-        if (lane == 0) wsum[warp] = __popc(bal);
-        __syncthreads();
-        unsigned before = 0;
-        for (int w = 0; w < warp; ++w) before += wsum[w];
-        if (mine) own[base + before + __popc(bal & ((1u << lane) - 1u))] = k;
-        __syncthreads();
-        if (threadIdx.x == 1023) base += before + __popc(bal);
-        __syncthreads();
+    const unsigned bal = __ballot_sync(0xffffffffu, mine);
+    if (lane == 0) wsum[warp] = __popc(bal);
+    __syncthreads();
+    unsigned before = 0, all = 0;
+    for (int w = 0; w < OWN_TILE / 32; ++w) {
+        const unsigned c = wsum[w];
+        before += w < warp ? c : 0u;
+        all += c;
     }
-    if (threadIdx.x == 0) *n_own = base;
+    *total = all;
+    return before + __popc(bal & ((1u << lane) - 1u));
+}
+
+__global__ void __launch_bounds__(OWN_TILE)
+    own_count_kernel(const unsigned *__restrict__ perm, unsigned n, unsigned own_begin,
+                     unsigned own_end, unsigned *__restrict__ counts)
+{
+    __shared__ unsigned wsum[OWN_TILE / 32];
+    const unsigned k = blockIdx.x * OWN_TILE + threadIdx.x;
+    const bool mine = k < n && perm[k] >= own_begin && perm[k] < own_end;
+    unsigned total;
+    own_rank_in_tile(mine, wsum, &total);
+    if (threadIdx.x == 0) counts[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(OWN_TILE)
+    own_write_kernel(const unsigned *__restrict__ perm, unsigned n, unsigned own_begin,
+                     unsigned own_end, const unsigned *__restrict__ base, unsigned *__restrict__ own)
+{
+    __shared__ unsigned wsum[OWN_TILE / 32];
+    const unsigned k = blockIdx.x * OWN_TILE + threadIdx.x;
+    const bool mine = k < n && perm[k] >= own_begin && perm[k] < own_end;
+    unsigned total;
+    const unsigned r = own_rank_in_tile(mine, wsum, &total);
+    if (mine) own[base[blockIdx.x] + r] = k;
 }
 
 // --------------------------------------------------------------- build ----
@@ -286,8 +304,11 @@ __device__ __forceinline__ double bh_inv_r3_times_m(double r2, double m)
     return fma(u, q, u);
 }
 
+#ifndef NB_BH_TRAV_MINB
+#define NB_BH_TRAV_MINB 10 // 48 registers, 40 warps per SM; 12 (40 regs, spills) and 16 measured slower
+#endif
 template <bool COUNT>
-__global__ void __launch_bounds__(TRAV_WARPS * 32) traverse_kernel(const TravArgs a)
+__global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_kernel(const TravArgs a)
 {
     __shared__ uint2 s_stack[TRAV_WARPS][TRAV_STACK]; // {cell id | depth << 27, lanes that must open it}
     __shared__ ChildRec s_child[TRAV_WARPS][8];
@@ -478,6 +499,7 @@ cudaError_t bh_alloc(BhTree *t, unsigned n)
     }
     BH_TRY(cudaMalloc(&t->spos, nn * sizeof(double4)));
     BH_TRY(cudaMalloc(&t->own, nn * sizeof(unsigned)));
+    BH_TRY(cudaMalloc(&t->own_counts, (nn / OWN_TILE + 2) * sizeof(unsigned)));
     BH_TRY(cudaMalloc(&t->com, (size_t)t->node_cap * sizeof(double4)));
     BH_TRY(cudaMalloc(&t->child, (size_t)t->node_cap * 8 * sizeof(int)));
     BH_TRY(cudaMalloc(&t->first, (size_t)t->node_cap * sizeof(unsigned)));
@@ -497,7 +519,7 @@ cudaError_t bh_alloc(BhTree *t, unsigned n)
 
 void bh_free(BhTree *t)
 {
-    void *bufs[] = {t->key[0], t->key[1], t->val[0], t->val[1], t->spos, t->own, t->com, t->child,
+    void *bufs[] = {t->key[0], t->key[1], t->val[0], t->val[1], t->spos, t->own, t->own_counts, t->com, t->child,
                     t->first, t->count, t->level, t->cblock, t->pslot, t->level_count, t->flags, t->bbox, t->hist,
                     t->counters};
     for (void *b : bufs)
@@ -522,8 +544,12 @@ cudaError_t bh_evaluate(BhTree *t, const BhParams &p, cudaStream_t s, unsigned *
     ++nl;
     const bool sliced = !(p.own_begin == 0 && p.own_end >= n);
     if (sliced) {
-        own_list_kernel<<<1, 1024, 0, s>>>(t->val[0], n, p.own_begin, p.own_end, t->own, &t->flags[2]);
-        ++nl;
+        const unsigned tiles = (n + OWN_TILE - 1) / OWN_TILE;
+        own_count_kernel<<<tiles, OWN_TILE, 0, s>>>(t->val[0], n, p.own_begin, p.own_end, t->own_counts);
+        BH_TRY(bh_exclusive_scan(t->own_counts, tiles, &t->flags[2], s));
+        own_write_kernel<<<tiles, OWN_TILE, 0, s>>>(t->val[0], n, p.own_begin, p.own_end,
+                                                    t->own_counts, t->own);
+        nl += 3;
     }
     if (n >= 2) {
         BuildArgs ba{t->key[0], t->first, t->count, t->level, t->child, t->level_count, t->flags,

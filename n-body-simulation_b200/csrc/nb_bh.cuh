@@ -17,9 +17,6 @@ namespace nb {
 
 constexpr int BH_MAX_LEVEL = 21; // 3 x 21 = 63 key bits; deeper cells become buckets
 
-// Device buffers of one engine's tree.  Bodies are referred to by their rank k
-// in Morton order ("sorted index"); perm[k] is the body's index in the state
-// arrays.
 // A child as the traversal sees it (64 bytes, 2 per 128-byte line).
 struct __align__(32) ChildRec {
     double4 c;  // body: x,y,z,m; cell: centre of mass + mass
@@ -28,6 +25,9 @@ struct __align__(32) ChildRec {
     int pad[5];
 };
 
+// Device buffers of one engine's tree.  Bodies are referred to by their rank k
+// in Morton order ("sorted index"); perm[k] is the body's index in the state
+// arrays.
 struct BhTree {
     unsigned n = 0;        // real bodies
     unsigned node_cap = 0; // internal-node pool size
@@ -36,6 +36,7 @@ struct BhTree {
     unsigned *val[2] = {nullptr, nullptr}; // body index, ping-pong; val[0] ends as perm
     double4 *spos = nullptr;               // x,y,z,m in Morton order
     unsigned *own = nullptr;               // sorted indices this rank integrates, Morton order
+    unsigned *own_counts = nullptr;        // per-tile member counts / bases of the compaction
     // per internal node
     double4 *com = nullptr;   // centre of mass x,y,z + total mass
     int *child = nullptr;     // [node][8]: -1 empty, >= 0 body (sorted index), <= -2 node -(c+2)
@@ -89,5 +90,7 @@ cudaError_t bh_stats(BhTree *t, BhStats *out, cudaStream_t s);
 // result in key[0], val[0].  bits: number of low key bits that matter.
 cudaError_t bh_radix_sort(BhTree *t, unsigned n, int bits, cudaStream_t s, unsigned *launches);
 unsigned bh_sort_blocks(unsigned n);
+// in-place exclusive prefix sum of `len` counters (one CTA); the grand total goes to *total
+cudaError_t bh_exclusive_scan(unsigned *a, unsigned len, unsigned *total, cudaStream_t s);
 
 } // namespace nb

@@ -156,6 +156,12 @@ __global__ void __launch_bounds__(SORT_THREADS)
 
 } // namespace
 
+cudaError_t bh_exclusive_scan(unsigned *a, unsigned len, unsigned *total, cudaStream_t s)
+{
+    scan_rows<<<1, 1024, 0, s>>>(a, len, total);
+    return cudaGetLastError();
+}
+
 unsigned bh_sort_blocks(unsigned n) { return n ? (n + SORT_TILE - 1) / SORT_TILE : 1u; }
 
 cudaError_t bh_radix_sort(BhTree *t, unsigned n, int bits, cudaStream_t s, unsigned *launches)
