@@ -210,6 +210,8 @@ def run_gpu_arm(args):
     prec = nb.PREC_FP32 if args.precision == "fp32" else nb.PREC_FP64
     n = args.bodies
     pm, vel = plummer(n)
+    if args.masses == "spread":
+        pm[:, 3] = np.random.default_rng(18).uniform(0.5, 1.5, n) / n
     eng = nb.Engine(pm, vel, precision=prec, device=local, rank=rank, world=world,
                     comm_id_bytes=comm, ctas_per_sm=args.ctas_per_sm, tune_flags=args.tune_flags)
     st0 = eng.stats()
@@ -298,7 +300,8 @@ def run_gpu_arm(args):
                 # FFMA 123.1 lane-ops/clk/SM; 6 FFMA2 + 1 MUFU (this kernel's mix) 12.5 clk per
                 # interaction-warp -> the mix's ceiling at sm_max_mhz
                 "peak_measured_ffma": SM_COUNT * 123.09 * 2 * SM_MAX_MHZ * 1e6 / 1e12,
-                "ceiling_of_instruction_mix": (SM_COUNT * 4 * 32 / 12.5 * SM_MAX_MHZ * 1e6
+                "ceiling_of_instruction_mix": (SM_COUNT * 4 * 32 / (12.5 * (11.0 / 12.0 if st0.uniform_mass else 1.0))
+                                               * SM_MAX_MHZ * 1e6
                                                * FLOP_PER_INTERACTION / 1e12) if prec == nb.PREC_FP32
                 else (SM_COUNT * 62.2 / 16.0 * SM_MAX_MHZ * 1e6 * FLOP_PER_INTERACTION / 1e12),
                 "traffic_note": "ncu dram__bytes_read+write per launch: profiles/ (kernel is FMA-bound, "
@@ -327,6 +330,10 @@ def run_gpu_arm(args):
                              "collectives": int(stb.collectives)},
             "roofline": roof,
             "grid": st0.grid, "block": st0.block,
+            "kernel": ("packed f32x2, equal masses: m_j hoisted out of the loop, 11 FMA-pipe ops + 1 MUFU "
+                       "per interaction" if eng.stats().uniform_mass else
+                       "packed f32x2, general masses: 12 FMA-pipe ops + 1 MUFU per interaction")
+            if prec == nb.PREC_FP32 else "fp64: 16 FP64-pipe ops + 1 MUFU per interaction",
         }
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
@@ -496,6 +503,9 @@ def main():
     ap.add_argument("--algorithm", default="direct", choices=["direct", "bh"],
                     help="direct = the headline exhaustive FP32 step; bh = Barnes-Hut (configs 4/5)")
     ap.add_argument("--no-accuracy", action="store_true")
+    ap.add_argument("--masses", default="equal", choices=["equal", "spread"],
+                    help="equal: m = 1/N (the Plummer model; the FP32 kernel hoists the mass "
+                         "multiply); spread: m ~ U(0.5, 1.5)/N, the general kernel")
     args = ap.parse_args()
     if args.algorithm == "bh" and args.impl != "reference":
         run_bh_arm(args)

@@ -11,7 +11,7 @@ namespace {
 
 __global__ void pack_f32_kernel(const double *__restrict__ pos, const double *__restrict__ vel,
                                 unsigned n, unsigned n_quads, float4 *__restrict__ q0,
-                                float4 *__restrict__ q1, float4 *__restrict__ v)
+                                float4 *__restrict__ q1, float4 *__restrict__ v, float pad_pos)
 {
     const unsigned iq = blockIdx.x * blockDim.x + threadIdx.x;
     if (iq >= n_quads) return;
@@ -20,9 +20,11 @@ __global__ void pack_f32_kernel(const double *__restrict__ pos, const double *__
     for (int r = 0; r < 4; ++r) {
         const unsigned b = iq * 4 + r;
         const bool real = b < n;
-        c[0][r] = real ? (float)pos[4 * (size_t)b + 0] : 0.f;
-        c[1][r] = real ? (float)pos[4 * (size_t)b + 1] : 0.f;
-        c[2][r] = real ? (float)pos[4 * (size_t)b + 2] : 0.f;
+        // padding: massless at the origin, or (uniform-mass kernels, which ignore m_j) so far
+        // away that r^-3 underflows to exactly 0
+        c[0][r] = real ? (float)pos[4 * (size_t)b + 0] : pad_pos;
+        c[1][r] = real ? (float)pos[4 * (size_t)b + 1] : pad_pos;
+        c[2][r] = real ? (float)pos[4 * (size_t)b + 2] : pad_pos;
         c[3][r] = real ? (float)pos[4 * (size_t)b + 3] : 0.f;
         c[4][r] = (real && vel) ? (float)vel[3 * (size_t)b + 0] : 0.f;
         c[5][r] = (real && vel) ? (float)vel[3 * (size_t)b + 1] : 0.f;
@@ -177,11 +179,11 @@ inline unsigned cdiv(unsigned a, unsigned b) { return (a + b - 1) / b; }
 } // namespace
 
 cudaError_t pack_bodies(int precision, const double *pos, const double *vel, unsigned n,
-                        unsigned n_units, void *q0, void *q1, void *v, cudaStream_t s)
+                        unsigned n_units, void *q0, void *q1, void *v, float pad_pos, cudaStream_t s)
 {
     if (precision == 1)
         pack_f32_kernel<<<cdiv(n_units, 256), 256, 0, s>>>(pos, vel, n, n_units, (float4 *)q0,
-                                                          (float4 *)q1, (float4 *)v);
+                                                          (float4 *)q1, (float4 *)v, pad_pos);
     else
         pack_f64_kernel<<<cdiv(n_units, 256), 256, 0, s>>>(pos, vel, n, n_units, (double4 *)q0,
                                                           (double4 *)q1, (double4 *)v);

@@ -6,8 +6,9 @@ namespace nb {
 
 // host packing (device copies of pos_xyzm[4n], vel_xyz[3n] or nullptr) -> device layout;
 // both position buffers are filled (masses and padding never change afterwards).
+// pad_pos: coordinate of the padding bodies (FP32 layout only; 0 = massless at the origin).
 cudaError_t pack_bodies(int precision, const double *pos, const double *vel, unsigned n,
-                        unsigned n_units, void *q0, void *q1, void *v, cudaStream_t s);
+                        unsigned n_units, void *q0, void *q1, void *v, float pad_pos, cudaStream_t s);
 // device layout -> host packing; planes = 4 (pos+mass) or 3 (vel / acc)
 cudaError_t unpack_bodies(int precision, const void *src, unsigned n, int planes, double *out,
                           cudaStream_t s);

@@ -119,6 +119,7 @@ struct StepParams {
     unsigned jt_begin;  // first j-tile of this launch (global tile index); tiles wrap modulo jt_total
     unsigned jt_total;  // j-tiles covering all n_units; ws.n_jtiles is this launch's share
     unsigned flags;
+    unsigned uniform_mass; // FP32: all masses equal -> kernels skip m_j; G below carries G * m
     double dt, eps2, G;
     WorkSplit ws;
 };

@@ -129,6 +129,8 @@ struct nb_engine {
     BhTree tree;            // NB_ALGO_BARNES_HUT only
     bool bh = false;
     bool count_visits = false;
+    bool uniform = false;   // FP32 direct: all masses equal (as floats) -> mass-free inner loop
+    double uniform_m = 0.0;
     State state = SYNCED_NOACC;
     void *comm = nullptr;
     bool vel_complete = true; // world > 1: do all ranks hold all velocities?
@@ -201,7 +203,8 @@ int launch_force(nb_engine *e, unsigned flags)
     p.flags = flags;
     p.dt = e->cfg.dt;
     p.eps2 = e->cfg.eps2;
-    p.G = e->cfg.G;
+    p.G = e->uniform ? e->cfg.G * e->uniform_m : e->cfg.G;
+    p.uniform_mass = e->uniform ? 1u : 0u;
     NB_CUDA(cudaEventRecord(e->ev_f0, e->stream));
     int rc;
     if (e->bh) {
@@ -279,8 +282,20 @@ int upload(nb_engine *e, const double *pos, const double *vel)
             NB_CUDA(cudaMemcpyAsync(e->stage_vel, vel, n * 3 * sizeof(double),
                                     cudaMemcpyHostToDevice, e->stream));
     }
+    // equal masses (the usual N-body initial condition): the FP32 kernel drops m_j from its inner
+    // loop and the epilogue multiplies by G*m.  Padding then has to be inert without a zero
+    // mass: it is parked so far away that r^-3 underflows to exactly 0.
+    e->uniform = false;
+    if (e->cfg.precision == NB_PREC_FP32 && !e->bh && n > 0 &&
+        !(e->cfg.tune_flags & (NB_TUNE_SCALAR_FP32 | NB_TUNE_NO_UNIFORM))) {
+        const float m0 = (float)pos[3];
+        bool same = m0 > 0.f;
+        for (size_t i = 1; i < n && same; ++i) same = (float)pos[4 * i + 3] == m0;
+        e->uniform = same;
+        e->uniform_m = (double)m0;
+    }
     NB_CUDA(pack_bodies(e->cfg.precision, e->stage_pos, vel ? e->stage_vel : nullptr, (unsigned)n,
-                        e->n_units, e->q[0], e->q[1], e->vel, e->stream));
+                        e->n_units, e->q[0], e->q[1], e->vel, e->uniform ? 1.0e18f : 0.f, e->stream));
     e->st.kernel_launches++;
     e->cur = 0;
     e->state = SYNCED_NOACC;
@@ -699,6 +714,7 @@ int nb_get_stats(nb_engine *e, nb_stats *out)
         NB_CUDA(cudaEventElapsedTime(&ms, e->ev_f0, e->ev_f1));
         e->st.last_force_ms = ms;
     }
+    e->st.uniform_mass = e->uniform ? 1 : 0;
     *out = e->st;
     return NB_OK;
 }

@@ -19,7 +19,7 @@ HOST_LIB_PATH = os.path.join(HERE, "libnbhost.so")
 PREC_FP64, PREC_FP32 = 0, 1
 ALGO_DIRECT, ALGO_BARNES_HUT = 0, 1
 COMM_ID_BYTES = 128
-TUNE_SCALAR_FP32, TUNE_NO_SPLIT, TUNE_NO_OVERLAP, TUNE_COUNT_VISITS = 1, 2, 4, 8
+TUNE_SCALAR_FP32, TUNE_NO_SPLIT, TUNE_NO_OVERLAP, TUNE_COUNT_VISITS, TUNE_NO_UNIFORM = 1, 2, 4, 8, 16
 SLICE_ALIGN = {PREC_FP32: 64, PREC_FP64: 128}  # units; nb_direct.cuh kSliceAlign*
 
 # every symbol include/nbody_engine.h declares
@@ -44,7 +44,7 @@ class NbStats(C.Structure):
                 ("grid", C.c_int), ("block", C.c_int), ("smem_bytes", C.c_int),
                 ("n", C.c_size_t), ("n_padded", C.c_size_t), ("slice_begin", C.c_size_t),
                 ("slice_end", C.c_size_t), ("collectives", C.c_ulonglong),
-                ("split_evaluations", C.c_ulonglong)]
+                ("split_evaluations", C.c_ulonglong), ("uniform_mass", C.c_int)]
 
 
 class NbTreeInfo(C.Structure):

@@ -243,3 +243,26 @@ def test_large_n_properties(nb, prec, n):
         lib.orc_acceleration_slice(n, pm, int(r), int(r) + 1, ref)
         err = np.linalg.norm(acc[r] - ref[0]) / np.linalg.norm(ref[0])
         assert err <= (1e-12 if prec == "fp64" else 1e-5)
+
+
+@pytest.mark.parametrize("n", [7, 1000, 10_000])
+def test_fp32_uniform_mass_path(nb, n):
+    """Equal masses: the FP32 kernel drops m_j from the inner loop (padding parked far away
+    instead of massless).  Same answers as the general kernel, to FP32 rounding."""
+    import oracle as O
+    g = golden("10k_bodies_g1")           # mass 0.2 everywhere
+    pm = g["pos_xyzm"][:n].astype(np.float32).astype(np.float64)
+    vel = g["vel"][:n].astype(np.float32).astype(np.float64)
+    ref = O.acceleration(O.load_oracle(), pm, "orc_acceleration_mt", 8)
+    outs = []
+    for flags in (0, nb.TUNE_NO_UNIFORM):
+        with nb.Engine(pm, vel, precision=nb.PREC_FP32, tune_flags=flags) as e:
+            acc = e.accelerations()
+            e.step(3)
+            outs.append((acc,) + e.gather())
+    for acc, p, v in outs:
+        assert rel_err(acc, ref).max() <= 1e-5
+        assert np.isfinite(p).all() and np.isfinite(v).all()
+        assert np.array_equal(p[:, 3], pm[:, 3])
+    assert rel_err(outs[0][0], outs[1][0]).max() <= 2e-6
+    assert rel_err(outs[0][1], outs[1][1]).max() <= 2e-6

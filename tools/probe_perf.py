@@ -35,6 +35,8 @@ def run(spec):
             flags |= int(o[8:]) << 8
         elif o.startswith("steps="):
             steps = int(o[6:])
+        elif o == "nouniform":
+            flags |= nb.TUNE_NO_UNIFORM
         elif o == "count":
             flags |= nb.TUNE_COUNT_VISITS
         elif o == "plummer":
