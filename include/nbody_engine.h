@@ -111,6 +111,21 @@ int nb_step(nb_engine *e, int n_steps);
  * positions only).  Blocks until the engine's stream is idle. */
 int nb_gather(nb_engine *e, double *pos_xyzm, double *vel_xyz);
 
+/* Frame pipeline for the RESULTS loop (serial/exhaustive.c:208-238 writes one
+ * frame per step; cuda/exhaustive.cu:153-165 reads every frame back with a
+ * blocking copy).  nb_frame_begin snapshots the current positions+mass
+ * (4n doubles) and starts copying them to pos_xyzm on a side stream, then
+ * returns; steps enqueued afterwards run while the copy lands and while the
+ * host formats the previous frame.  nb_frame_wait blocks until the snapshot
+ * headed for pos_xyzm is complete (NULL: every outstanding snapshot).  Two
+ * snapshots can be in flight.  pos_xyzm should come from nb_host_alloc
+ * (page-locked), otherwise the copy is staged by the driver and does not
+ * overlap. */
+int nb_frame_begin(nb_engine *e, double *pos_xyzm);
+int nb_frame_wait(nb_engine *e, const double *pos_xyzm);
+int nb_host_alloc(void **p, size_t bytes);
+int nb_host_free(void *p);
+
 /* acceleration() on the current positions (serial/exhaustive.c:155-181,
  * cuda/exhaustive.cu:273-338, or the Barnes-Hut evaluation): acc_xyz[3n].
  * Does not advance the state. */

@@ -128,35 +128,64 @@ __global__ void kickdrift_f64_kernel(const double4 *__restrict__ qc, double4 *__
 // contribute 0, common/get_energy.c:38-40).  One thread per i, j > i tiles in
 // shared memory, block partials written out and added on the host in order.
 constexpr int ETB = 256;
-__global__ void energy_kernel(const double *__restrict__ pos, const double *__restrict__ vel,
-                              unsigned n, double *__restrict__ partial /* [grid][2] */)
+
+// 1/r from MUFU.RSQ64H + one cubically convergent step (relative error < 2^-58); 0 for r = 0
+__device__ __forceinline__ double inv_r(double r2)
+{
+    double y0;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y0) : "d"(r2));
+    const double e = fma(-r2 * y0, y0, 1.0);
+    const double y = fma(y0 * e, fma(0.375, e, 0.5), y0);
+    return r2 > 0.0 ? y : 0.0;
+}
+
+// Rows of tile t against all j > i.  Row tiles near the top of the triangle have many
+// columns, those near the bottom few: a CTA takes tile b and tile (last - b), so all CTAs
+// carry the same number of pairs.
+__global__ void __launch_bounds__(ETB)
+    energy_kernel(const double *__restrict__ pos, const double *__restrict__ vel, unsigned n,
+                  double *__restrict__ partial /* [grid][2] */)
 {
     __shared__ double4 tile[ETB];
     __shared__ double red[2][ETB / 32];
-    const unsigned i = blockIdx.x * ETB + threadIdx.x;
-    const bool real = i < n;
-    double xi = 0, yi = 0, zi = 0, mi = 0, ke = 0, pe = 0;
-    if (real) {
-        xi = pos[4 * (size_t)i]; yi = pos[4 * (size_t)i + 1]; zi = pos[4 * (size_t)i + 2];
-        mi = pos[4 * (size_t)i + 3];
-        const double vx = vel[3 * (size_t)i], vy = vel[3 * (size_t)i + 1], vz = vel[3 * (size_t)i + 2];
-        ke = mi * (vx * vx + vy * vy + vz * vz);
-    }
-    for (unsigned j0 = blockIdx.x * ETB; j0 < n; j0 += ETB) {
-        const unsigned j = j0 + threadIdx.x;
-        tile[threadIdx.x] = j < n ? make_double4(pos[4 * (size_t)j], pos[4 * (size_t)j + 1],
-                                                 pos[4 * (size_t)j + 2], pos[4 * (size_t)j + 3])
-                                  : make_double4(0, 0, 0, 0);
-        __syncthreads();
-        const unsigned lim = min((unsigned)ETB, n - j0);
-        for (unsigned k = 0; k < lim; ++k) {
-            if (j0 + k <= i) continue;
-            const double4 b = tile[k];
-            const double dx = b.x - xi, dy = b.y - yi, dz = b.z - zi;
-            const double r = sqrt(dx * dx + dy * dy + dz * dz);
-            pe += r > 0 ? (mi * b.w) / r : 0.0;
+    const unsigned ntiles = (n + ETB - 1) / ETB;
+    double ke = 0, pe = 0;
+    for (int half = 0; half < 2; ++half) {
+        const unsigned t = half == 0 ? blockIdx.x : ntiles - 1 - blockIdx.x;
+        if (half == 1 && t <= blockIdx.x) break; // odd tile count: the middle tile is done once
+        const unsigned i = t * ETB + threadIdx.x;
+        const bool real = i < n;
+        double xi = 0, yi = 0, zi = 0, mi = 0, pei = 0;
+        if (real) {
+            xi = pos[4 * (size_t)i]; yi = pos[4 * (size_t)i + 1]; zi = pos[4 * (size_t)i + 2];
+            mi = pos[4 * (size_t)i + 3];
+            const double vx = vel[3 * (size_t)i], vy = vel[3 * (size_t)i + 1], vz = vel[3 * (size_t)i + 2];
+            ke += mi * (vx * vx + vy * vy + vz * vz);
         }
-        __syncthreads();
+        for (unsigned j0 = t * ETB; j0 < n; j0 += ETB) {
+            const unsigned j = j0 + threadIdx.x;
+            __syncthreads();
+            tile[threadIdx.x] = j < n ? make_double4(pos[4 * (size_t)j], pos[4 * (size_t)j + 1],
+                                                     pos[4 * (size_t)j + 2], pos[4 * (size_t)j + 3])
+                                      : make_double4(0, 0, 0, 0);
+            __syncthreads();
+            const unsigned lim = min((unsigned)ETB, n - j0);
+            if (j0 == t * ETB) { // diagonal tile: j > i only
+                for (unsigned k = threadIdx.x + 1; k < lim; ++k) {
+                    const double4 b = tile[k];
+                    const double dx = b.x - xi, dy = b.y - yi, dz = b.z - zi;
+                    pei = fma(b.w, inv_r(fma(dz, dz, fma(dy, dy, dx * dx))), pei);
+                }
+            } else {
+#pragma unroll 4
+                for (unsigned k = 0; k < lim; ++k) {
+                    const double4 b = tile[k];
+                    const double dx = b.x - xi, dy = b.y - yi, dz = b.z - zi;
+                    pei = fma(b.w, inv_r(fma(dz, dz, fma(dy, dy, dx * dx))), pei);
+                }
+            }
+        }
+        if (real) pe += mi * pei;
     }
     for (int o = 16; o > 0; o >>= 1) {
         ke += __shfl_xor_sync(0xffffffffu, ke, o);
@@ -217,7 +246,7 @@ cudaError_t kickdrift(int precision, const void *qc, void *qn, void *vel, const 
     return cudaGetLastError();
 }
 
-unsigned energy_blocks(unsigned n) { return cdiv(n, ETB); }
+unsigned energy_blocks(unsigned n) { return cdiv(cdiv(n, ETB), 2); } // a CTA takes two row tiles
 
 cudaError_t energy_partials(const double *pos_xyzm, const double *vel_xyz, unsigned n,
                             double *partial, cudaStream_t s)

@@ -125,6 +125,13 @@ struct nb_engine {
     unsigned *counters = nullptr;
     double *stage_pos = nullptr, *stage_vel = nullptr; // host-packing staging, n*4 / n*3 doubles
     double *energy_part = nullptr;
+    // frame pipeline (nb_frame_begin / nb_frame_wait), created on first use
+    cudaStream_t copy_stream = nullptr;
+    double *frame_stage[2] = {nullptr, nullptr};                  // unpacked snapshots, 4n doubles
+    cudaEvent_t ev_frame_ready[2] = {nullptr, nullptr};           // snapshot written (compute stream)
+    cudaEvent_t ev_frame_done[2] = {nullptr, nullptr};            // copied to the host (copy stream)
+    const double *frame_host[2] = {nullptr, nullptr};             // where each slot is headed
+    unsigned frame_seq = 0;
     DirectPlan plan;
     BhTree tree;            // NB_ALGO_BARNES_HUT only
     bool bh = false;
@@ -371,12 +378,16 @@ void nb_free(nb_engine *e)
     if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
     bh_free(&e->tree);
     void *bufs[] = {e->q[0], e->q[1], e->vel, e->acc, e->workspace, e->partial, e->counters,
-                    e->stage_pos, e->stage_vel, e->energy_part};
+                    e->stage_pos, e->stage_vel, e->energy_part, e->frame_stage[0], e->frame_stage[1]};
+    if (e->copy_stream) cudaStreamSynchronize(e->copy_stream);
     for (void *b : bufs)
         if (b) cudaFree(b);
-    cudaEvent_t evs[] = {e->ev_step0, e->ev_step1, e->ev_f0, e->ev_f1, e->ev_compute, e->ev_gather};
+    cudaEvent_t evs[] = {e->ev_step0, e->ev_step1, e->ev_f0, e->ev_f1, e->ev_compute, e->ev_gather,
+                         e->ev_frame_ready[0], e->ev_frame_ready[1], e->ev_frame_done[0],
+                         e->ev_frame_done[1]};
     for (cudaEvent_t ev : evs)
         if (ev) cudaEventDestroy(ev);
+    if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
     if (e->comm_stream) cudaStreamDestroy(e->comm_stream);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;
@@ -571,6 +582,68 @@ int nb_sync(nb_engine *e)
     if (rc) return rc;
     NB_CUDA(cudaStreamSynchronize(e->stream));
     if (e->comm_stream) NB_CUDA(cudaStreamSynchronize(e->comm_stream));
+    if (e->copy_stream) NB_CUDA(cudaStreamSynchronize(e->copy_stream));
+    return NB_OK;
+}
+
+int nb_frame_begin(nb_engine *e, double *pos_xyzm)
+{
+    if (!e || !pos_xyzm) return NB_E_INVALID;
+    int rc = set_device(e);
+    if (rc) return rc;
+    const unsigned n = (unsigned)e->n;
+    if (!e->copy_stream) {
+        NB_CUDA(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+        for (int k = 0; k < 2; ++k) {
+            NB_CUDA(cudaMalloc(&e->frame_stage[k], (size_t)(n ? n : 1) * 4 * sizeof(double)));
+            NB_CUDA(cudaEventCreateWithFlags(&e->ev_frame_ready[k], cudaEventDisableTiming));
+            NB_CUDA(cudaEventCreateWithFlags(&e->ev_frame_done[k], cudaEventDisableTiming));
+        }
+    }
+    rc = wait_gather(e); // every rank's positions of this step are in place
+    if (rc) return rc;
+    const int k = (int)(e->frame_seq++ & 1u);
+    // the slot's previous snapshot must have left the device before it is overwritten
+    if (e->frame_host[k]) NB_CUDA(cudaStreamWaitEvent(e->stream, e->ev_frame_done[k], 0));
+    NB_CUDA(unpack_bodies(e->cfg.precision, e->q[e->cur], n, 4, e->frame_stage[k], e->stream));
+    e->st.kernel_launches++;
+    NB_CUDA(cudaEventRecord(e->ev_frame_ready[k], e->stream));
+    NB_CUDA(cudaStreamWaitEvent(e->copy_stream, e->ev_frame_ready[k], 0));
+    if (n)
+        NB_CUDA(cudaMemcpyAsync(pos_xyzm, e->frame_stage[k], (size_t)n * 4 * sizeof(double),
+                                cudaMemcpyDeviceToHost, e->copy_stream));
+    NB_CUDA(cudaEventRecord(e->ev_frame_done[k], e->copy_stream));
+    e->frame_host[k] = pos_xyzm;
+    return NB_OK;
+}
+
+int nb_frame_wait(nb_engine *e, const double *pos_xyzm)
+{
+    if (!e) return NB_E_INVALID;
+    int rc = set_device(e);
+    if (rc) return rc;
+    if (!e->copy_stream) return NB_OK; // nothing was ever started
+    bool known = false;
+    for (int k = 0; k < 2; ++k)
+        if (pos_xyzm && e->frame_host[k] == pos_xyzm) {
+            NB_CUDA(cudaEventSynchronize(e->ev_frame_done[k]));
+            known = true;
+        }
+    if (!known) NB_CUDA(cudaStreamSynchronize(e->copy_stream)); // NULL or an older snapshot
+    return NB_OK;
+}
+
+int nb_host_alloc(void **p, size_t bytes)
+{
+    if (!p) return NB_E_INVALID;
+    *p = nullptr;
+    NB_CUDA(cudaHostAlloc(p, bytes ? bytes : 1, cudaHostAllocDefault));
+    return NB_OK;
+}
+
+int nb_host_free(void *p)
+{
+    if (p) NB_CUDA(cudaFreeHost(p));
     return NB_OK;
 }
 

@@ -110,13 +110,29 @@ int main(int argc, char *argv[])
         }
         if (initial_frame)
             nbh_write_frame(fpt, n_ents, positions); /* frame 0 = initial state */
-        for (int t = 0; t < n_steps; t++) {
-            if ((rc = nb_step(eng, 1)))
-                die_engine("nb_step", rc);
-            if ((rc = nb_gather(eng, positions, NULL)))
-                die_engine("nb_gather", rc);
-            nbh_write_frame(fpt, n_ents, positions);
+        /* The reference reads every frame back with a blocking copy and formats it
+         * while the GPU idles (cuda/exhaustive.cu:135-165).  Here step t+1 is
+         * enqueued before frame t is waited for, so the kernel, the copy (side
+         * stream, page-locked buffers) and the formatting overlap. */
+        double *frame[2] = {NULL, NULL};
+        for (int k = 0; k < 2; k++)
+            if ((rc = nb_host_alloc((void **)&frame[k], (n_ents ? n_ents : 1) * 4 * sizeof(double))))
+                die_engine("nb_host_alloc", rc);
+        for (int t = 0; t <= n_steps; t++) {
+            if (t < n_steps) {
+                if ((rc = nb_step(eng, 1)))
+                    die_engine("nb_step", rc);
+                if ((rc = nb_frame_begin(eng, frame[t & 1])))
+                    die_engine("nb_frame_begin", rc);
+            }
+            if (t > 0) {
+                if ((rc = nb_frame_wait(eng, frame[(t - 1) & 1])))
+                    die_engine("nb_frame_wait", rc);
+                nbh_write_frame(fpt, n_ents, frame[(t - 1) & 1]);
+            }
         }
+        nb_host_free(frame[0]);
+        nb_host_free(frame[1]);
         fclose(fpt);
     } else {
         if (n_steps > 0 && (rc = nb_step(eng, n_steps)))

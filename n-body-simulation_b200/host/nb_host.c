@@ -3,6 +3,9 @@
  * programs (see nb_host.h for the reference lines each routine follows).
  */
 #include "nb_host.h"
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 #include <ctype.h>
 #include <stdint.h>
@@ -229,23 +232,10 @@ size_t nbh_format_frame(char *buf, size_t cap, size_t n, const double *pm)
     return k;
 }
 
-int nbh_write_frame(FILE *fp, size_t n, const double *pm)
+static size_t format_lines(char *buf, size_t first, size_t last, const double *pm)
 {
-    enum { CHUNK = 4096 };
-    static char *buf = NULL;
-    if (!buf) {
-        buf = malloc((size_t)CHUNK * 128 + NBH_LINE_MAX);
-        if (!buf)
-            return NBH_ENOMEM;
-    }
-    const size_t cap = (size_t)CHUNK * 128 + NBH_LINE_MAX;
     size_t k = 0;
-    for (size_t i = 0; i < n; i++) {
-        if (cap - k < NBH_LINE_MAX) {
-            if (fwrite(buf, 1, k, fp) != k)
-                return NBH_EOPEN;
-            k = 0;
-        }
+    for (size_t i = first; i < last; i++) {
         k += put_u64(buf + k, (uint64_t)i);
         for (int c = 0; c < 4; c++) {
             buf[k++] = ',';
@@ -253,8 +243,43 @@ int nbh_write_frame(FILE *fp, size_t n, const double *pm)
         }
         buf[k++] = '\n';
     }
-    if (k && fwrite(buf, 1, k, fp) != k)
-        return NBH_EOPEN;
+    return k;
+}
+
+/* Lines are formatted CHUNK bodies at a time; with OpenMP the chunks of one round go to
+ * different threads and are written out in body order, so the file is the same byte for
+ * byte whatever the thread count (OMP_NUM_THREADS=1 gives the serial writer). */
+int nbh_write_frame(FILE *fp, size_t n, const double *pm)
+{
+    enum { CHUNK = 1024, MAXT = 32 };
+    static char *buf[MAXT];
+    int nt = 1;
+#ifdef _OPENMP
+    nt = omp_get_max_threads();
+#endif
+    if (nt > MAXT)
+        nt = MAXT;
+    if ((size_t)nt > (n + CHUNK - 1) / CHUNK)
+        nt = (int)((n + CHUNK - 1) / CHUNK);
+    if (nt < 1)
+        nt = 1;
+    for (int t = 0; t < nt; t++)
+        if (!buf[t] && !(buf[t] = malloc((size_t)CHUNK * NBH_LINE_MAX)))
+            return NBH_ENOMEM;
+    size_t len[MAXT];
+    for (size_t base = 0; base < n; base += (size_t)nt * CHUNK) {
+#ifdef _OPENMP
+#pragma omp parallel for num_threads(nt) schedule(static, 1) if (nt > 1)
+#endif
+        for (int t = 0; t < nt; t++) {
+            const size_t first = base + (size_t)t * CHUNK;
+            const size_t last = first + CHUNK < n ? first + CHUNK : n;
+            len[t] = first < n ? format_lines(buf[t], first, last, pm) : 0;
+        }
+        for (int t = 0; t < nt; t++)
+            if (len[t] && fwrite(buf[t], 1, len[t], fp) != len[t])
+                return NBH_EOPEN;
+    }
     return NBH_OK;
 }
 

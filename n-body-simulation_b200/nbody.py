@@ -24,6 +24,7 @@ SLICE_ALIGN = {PREC_FP32: 64, PREC_FP64: 128}  # units; nb_direct.cuh kSliceAlig
 
 # every symbol include/nbody_engine.h declares
 ABI_SYMBOLS = ["nb_config_default", "nb_init", "nb_upload", "nb_step", "nb_gather",
+               "nb_frame_begin", "nb_frame_wait", "nb_host_alloc", "nb_host_free",
                "nb_accelerations", "nb_energy", "nb_sync", "nb_get_stats", "nb_tree_stats", "nb_free",
                "nb_comm_id", "nb_strerror", "nb_last_error", "nb_device_count", "nb_version"]
 HOST_SYMBOLS = ["nbh_read_bodies", "nbh_parse_bodies", "nbh_free", "nbh_parse_times",
@@ -80,6 +81,10 @@ def load_library():
     lib.nb_upload.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     lib.nb_step.argtypes = [C.c_void_p, C.c_int]
     lib.nb_gather.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.nb_frame_begin.argtypes = [C.c_void_p, C.c_void_p]
+    lib.nb_frame_wait.argtypes = [C.c_void_p, C.c_void_p]
+    lib.nb_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
+    lib.nb_host_free.argtypes = [C.c_void_p]
     lib.nb_accelerations.argtypes = [C.c_void_p, C.c_void_p]
     lib.nb_energy.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.nb_sync.argtypes = [C.c_void_p]
@@ -191,6 +196,7 @@ class Engine:
             cfg.comm_id = C.cast(self._idbuf, C.c_void_p)
         self.cfg = cfg
         self.handle = C.c_void_p()
+        self._pinned = []
         _check(self.lib, self.lib.nb_init(C.byref(self.handle), C.byref(cfg), self.n,
                                           pos.ctypes.data, vel.ctypes.data), "nb_init")
 
@@ -211,6 +217,23 @@ class Engine:
         _check(self.lib, self.lib.nb_gather(self.handle, pos.ctypes.data,
                                             vel.ctypes.data if with_velocities else None), "nb_gather")
         return pos, vel
+
+    def frame_buffer(self):
+        """a page-locked (n, 4) float64 array for frame_begin (nb_host_alloc); freed with the engine"""
+        p = C.c_void_p()
+        _check(self.lib, self.lib.nb_host_alloc(C.byref(p), max(self.n, 1) * 32), "nb_host_alloc")
+        self._pinned.append(p)
+        buf = (C.c_double * (self.n * 4)).from_address(p.value)
+        return np.frombuffer(buf, dtype=np.float64).reshape(self.n, 4)
+
+    def frame_begin(self, out):
+        """starts the asynchronous read-back of the current positions into `out` ((n, 4) float64)"""
+        assert out.dtype == np.float64 and out.flags.c_contiguous and out.size == self.n * 4
+        _check(self.lib, self.lib.nb_frame_begin(self.handle, out.ctypes.data), "nb_frame_begin")
+
+    def frame_wait(self, out=None):
+        _check(self.lib, self.lib.nb_frame_wait(self.handle, out.ctypes.data if out is not None else None),
+               "nb_frame_wait")
 
     def gather_raw(self, pos_ptr, vel_ptr):
         _check(self.lib, self.lib.nb_gather(self.handle, pos_ptr, vel_ptr), "nb_gather")
@@ -242,6 +265,9 @@ class Engine:
         if self.handle:
             self.lib.nb_free(self.handle)
             self.handle = C.c_void_p()
+            for p in self._pinned:  # arrays from frame_buffer() die with the engine
+                self.lib.nb_host_free(p)
+            self._pinned = []
 
     def __enter__(self):
         return self
