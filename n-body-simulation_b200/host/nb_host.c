@@ -24,18 +24,21 @@ static size_t skip_ws(const char *t, size_t p, size_t len)
 }
 
 /*
- * Single pass over the text.  A record is seven numbers; what may sit between
+ * One pass over text[p, len).  A record is seven numbers; what may sit between
  * them is exactly what the reference's scanf format allows: "<num>," then
  * optional white space before the next number, and optional white space after
  * the seventh.  `p` always points at the first byte scanf would not have
  * consumed, so "bytes left at p" is the reference's fgetc() != EOF test.
+ * *partial: numbers of an unfinished record consumed at the end of the range.
  */
-int nbh_parse_bodies(const char *text, size_t len, size_t *n_out, double **pos_out,
-                     double **vel_out)
+static int parse_range(const char *text, size_t p, size_t len, size_t *n_out, double **pos_out,
+                       double **vel_out, int *partial)
 {
-    size_t cap = 1024, n = 0, p = 0;
+    size_t cap = 1024, n = 0;
     double *pos = malloc(cap * 4 * sizeof(double));
     double *vel = malloc(cap * 3 * sizeof(double));
+    *partial = 0;
+    *pos_out = *vel_out = NULL;
     if (!pos || !vel) {
         free(pos);
         free(vel);
@@ -61,8 +64,10 @@ int nbh_parse_bodies(const char *text, size_t len, size_t *n_out, double **pos_o
                 p++;
             }
         }
-        if (got != 7)
+        if (got != 7) {
+            *partial = got;
             break;
+        }
         p = skip_ws(text, p, len); /* the "\n" directive: any white space */
         if (n == cap) {
             cap *= 2;
@@ -94,6 +99,94 @@ int nbh_parse_bodies(const char *text, size_t len, size_t *n_out, double **pos_o
     *pos_out = pos;
     *vel_out = vel;
     return NBH_OK;
+}
+
+/*
+ * Large inputs are cut after a line feed into one range per thread and the
+ * ranges parsed side by side.  The scanf grammar does not care about lines, so
+ * a cut can fall inside a record ("1,2,3,\n4,5,6,7"): a range that is not a
+ * whole number of records (or fails in any way) sends the whole text through
+ * the serial parser, whose verdict is the reference's.  When every range is
+ * clean, the serial parser would have reached each cut at a record boundary
+ * too (a number cannot span a line feed), so the result is the same.
+ */
+#define NBH_PAR_MIN_BYTES (4u << 20)
+#define NBH_PAR_MAX 64
+
+int nbh_parse_bodies(const char *text, size_t len, size_t *n_out, double **pos_out,
+                     double **vel_out)
+{
+    int partial, nt = 1;
+#ifdef _OPENMP
+    nt = omp_get_max_threads();
+#endif
+    if (nt > NBH_PAR_MAX)
+        nt = NBH_PAR_MAX;
+    if (len / NBH_PAR_MIN_BYTES < (size_t)nt)
+        nt = (int)(len / NBH_PAR_MIN_BYTES);
+    if (nt >= 2) {
+        size_t cut[NBH_PAR_MAX + 1], cnt[NBH_PAR_MAX];
+        double *ppos[NBH_PAR_MAX], *pvel[NBH_PAR_MAX];
+        int rcs[NBH_PAR_MAX], part[NBH_PAR_MAX];
+        cut[0] = 0;
+        cut[nt] = len;
+        for (int t = 1; t < nt; t++) {
+            size_t c = len / (size_t)nt * (size_t)t;
+            if (c < cut[t - 1])
+                c = cut[t - 1];
+            const char *nl = memchr(text + c, '\n', len - c);
+            cut[t] = nl ? (size_t)(nl - text) + 1 : len;
+        }
+#ifdef _OPENMP
+#pragma omp parallel for num_threads(nt) schedule(static, 1)
+#endif
+        for (int t = 0; t < nt; t++)
+            rcs[t] = parse_range(text, cut[t], cut[t + 1], &cnt[t], &ppos[t], &pvel[t], &part[t]);
+        int clean = 1;
+        size_t total = 0;
+        for (int t = 0; t < nt; t++) {
+            if (rcs[t] != NBH_OK || (part[t] && t < nt - 1))
+                clean = 0;
+            else
+                total += cnt[t];
+        }
+        double *pos = NULL, *vel = NULL;
+        if (clean) {
+            pos = malloc((total ? total : 1) * 4 * sizeof(double));
+            vel = malloc((total ? total : 1) * 3 * sizeof(double));
+            if (!pos || !vel) {
+                free(pos);
+                free(vel);
+                pos = vel = NULL;
+                clean = 0;
+            }
+        }
+        if (clean) {
+            size_t off[NBH_PAR_MAX];
+            off[0] = 0;
+            for (int t = 1; t < nt; t++)
+                off[t] = off[t - 1] + cnt[t - 1];
+#ifdef _OPENMP
+#pragma omp parallel for num_threads(nt) schedule(static, 1)
+#endif
+            for (int t = 0; t < nt; t++) {
+                memcpy(pos + 4 * off[t], ppos[t], cnt[t] * 4 * sizeof(double));
+                memcpy(vel + 3 * off[t], pvel[t], cnt[t] * 3 * sizeof(double));
+            }
+        }
+        for (int t = 0; t < nt; t++)
+            if (rcs[t] == NBH_OK) {
+                free(ppos[t]);
+                free(pvel[t]);
+            }
+        if (clean) {
+            *n_out = total;
+            *pos_out = pos;
+            *vel_out = vel;
+            return NBH_OK;
+        }
+    }
+    return parse_range(text, 0, len, n_out, pos_out, vel_out, &partial);
 }
 
 int nbh_read_bodies(const char *path, size_t *n, double **pos_xyzm, double **vel_xyz)

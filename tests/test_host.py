@@ -148,3 +148,32 @@ def test_slice_bounds_partition(nb):
                 if world > 1:
                     unit = 4 if prec == nb.PREC_FP32 else 1
                     assert all((x[0] % (nb.SLICE_ALIGN[prec] * unit) == 0) or x[0] == n for x in b)
+
+
+def test_reader_parallel_ranges_equal_serial_rules(nb, tmp_path):
+    """Inputs over 8 MB are parsed in per-thread ranges cut after a line feed; a cut inside a
+    record (the scanf grammar allows line feeds between the fields) or an error anywhere falls
+    back to the serial parser, so the result never depends on the thread count."""
+    rng = np.random.default_rng(11)
+    n = 120_000
+    rows = np.concatenate([rng.standard_normal((n, 6)) * 10, rng.uniform(0.5, 2, (n, 1))], axis=1)
+    lines = [",".join("%.17g" % x for x in r) for r in rows]
+    path = str(tmp_path / "big.csv")
+    open(path, "w").write("\n".join(lines) + "\n")
+    assert os.path.getsize(path) > (8 << 20)
+    pos, vel = nb.read_bodies(path)
+    assert np.array_equal(pos, rows[:, [0, 1, 2, 6]]) and np.array_equal(vel, rows[:, 3:6])
+    # every record broken over two lines: whatever the cuts hit, the bodies are the same
+    open(path, "w").write("\n".join(l.replace(",", ",\n", 3).replace(",\n", ",", 2) for l in lines))
+    pos2, vel2 = nb.read_bodies(path)
+    assert np.array_equal(pos2, pos) and np.array_equal(vel2, vel)
+    # a malformed record in the middle is still an error
+    bad = list(lines)
+    bad[n // 2 + 17] = bad[n // 2 + 17].replace(",", ";", 1)
+    open(path, "w").write("\n".join(bad) + "\n")
+    with pytest.raises(ValueError):
+        nb.read_bodies(path)
+    # a truncated last record is dropped, as fscanf's short count does in the reference
+    open(path, "w").write("\n".join(lines) + "\n1,2,3,")
+    pos3, _ = nb.read_bodies(path)
+    assert np.array_equal(pos3, pos)
