@@ -198,14 +198,30 @@ __global__ void __launch_bounds__(BH_THREADS) build_level_kernel(BuildArgs a, in
             r.c = a.spos[start];
             r.b2 = -1.0;
             r.ent = (int)start;
+            r.code = 0;
             a.cblock[at] = r;
         } else if (ch <= -2) {
-            a.cblock[at].ent = ch;           // centre of mass and border^2 follow in com_level_kernel
+            // centre of mass and border^2 follow in com_level_kernel, the child count when the
+            // child itself is split (next level)
+            a.cblock[at].ent = ch;
+            a.cblock[at].code = (int)((unsigned)(-ch - 2) | (L + 1 == BH_MAX_LEVEL ? BH_CODE_BUCKET : 0u));
             a.pslot[-ch - 2] = at;
         } else if (k >= 2) {
-            a.cblock[at].ent = -1;           // node pool exhausted: the list ends here (flagged)
+            // node pool exhausted (flagged, the result is refused): a massless stand-in keeps
+            // the walk inside valid memory
+            ChildRec r;
+            r.c = a.spos[start];
+            r.c.w = 0.0;
+            r.b2 = -1.0;
+            r.ent = (int)start;
+            r.code = 0;
+            a.cblock[at] = r;
         }
-        if (oct == 7 && __popc(nonempty) < 8) a.cblock[nd * 8u + __popc(nonempty)].ent = -1;
+        if (oct == 0) { // how many records the walk reads when it opens this node
+            const unsigned code = nd | ((unsigned)(__popc(nonempty) - 1) << BH_CODE_NC_SHIFT);
+            if (nd == 0) a.flags[3] = code;
+            else a.cblock[a.pslot[nd]].code = (int)code;
+        }
     }
 }
 
@@ -267,11 +283,16 @@ __global__ void __launch_bounds__(BH_THREADS)
 // drops out of its subtree.  Each body therefore sees exactly the serial
 // reference's interaction list, in the reference's order (children 0..7,
 // depth first), and agrees with it to rounding, not just within the THETA
-// envelope.  An opened cell's eight children are fetched by eight lanes at once
-// and tested in one go (one memory round trip per OPENED cell instead of one per
-// visited node); only cells that some lane must open go through the stack.  The
-// sum order therefore is "a cell's accepted children first, then its opened
-// children's subtrees" -- the reference's terms, regrouped.
+// envelope.  An opened cell's child records (one 512-byte block) are fetched by
+// the warp in one coalesced copy and tested in one go (one memory round trip per
+// OPENED cell instead of one per visited node); only cells that some lane must
+// open go through the stack.  The sum order therefore is "a cell's accepted
+// children first, then its opened children's subtrees" -- the reference's terms,
+// regrouped.  The loop over a cell's children is straight-line code (no vote, no
+// branch per child: ncu showed the walk bound by issue slots, 45 instructions per
+// child of which 19 FP64): every lane computes the interaction and adds it under
+// a select, and records in a bit mask what it did not take; the votes happen once
+// per cell, only for the children that some lane must open.
 //
 // Acceptance is tested as border^2 < THETA^2 * dist^2 -- the reference's
 // border / dist < THETA (:405) without the FP64 divide and square root; the two
@@ -305,13 +326,13 @@ __device__ __forceinline__ double bh_inv_r3_times_m(double r2, double m)
 }
 
 #ifndef NB_BH_TRAV_MINB
-#define NB_BH_TRAV_MINB 10 // 48 registers, 40 warps per SM; 12 (40 regs, spills) and 16 measured slower
+#define NB_BH_TRAV_MINB 8 // 64 registers, 32 warps per SM: no spills, constants stay in registers; 10 (48 regs) measured 7 % slower
 #endif
 template <bool COUNT>
 __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_kernel(const TravArgs a)
 {
     __shared__ uint2 s_stack[TRAV_WARPS][TRAV_STACK]; // {cell id | depth << 27, lanes that must open it}
-    __shared__ ChildRec s_child[TRAV_WARPS][8];
+    __shared__ ChildRec s_child[TRAV_WARPS][2][8];
     __shared__ double s_border2[BH_MAX_LEVEL + 2];
     if (threadIdx.x <= BH_MAX_LEVEL) {
         double b = 2.0 * a.bbox[0]; // root border = max (serial/barnes-hut.c:470), halved per level
@@ -334,38 +355,39 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
     double ax = 0, ay = 0, az = 0;
     unsigned n_inter = 0, n_visit = 0;
     uint2 *stk = s_stack[warp];
-    ChildRec *slot = s_child[warp];
+    int flip = 0;
     int sp = 0;
     const unsigned all = __ballot_sync(0xffffffffu, valid);
 
-    // One candidate (a body or a cell) against the warp's 32 bodies, for the lanes in M.
-    // A lane takes it if it is far enough (border^2 < THETA^2 dist^2; bodies carry border^2 = -1)
-    // and it is not the lane's own body (:411).  Returns the lanes that took it; for a cell the
-    // others of M must open it.  Branch-free per lane: a lane that does not take the
-    // interaction multiplies by a zero mass.
-    auto consider = [&](const double4 &c, double b2, int ent, unsigned M) -> unsigned {
+    // One candidate (a body or a cell) against the warp's 32 bodies.  A lane takes it if it is
+    // one of the lanes the candidate is meant for (`mine`), it is far enough (border^2 <
+    // THETA^2 dist^2; bodies carry border^2 = -1) and it is not the lane's own body (:411).
+    // Returns whether the lane took it; for a cell the other lanes it was meant for must open
+    // it.  Straight-line code: the interaction is computed by every lane and added under a
+    // predicate -- the walk is bound by issue slots, and a vote plus a branch per candidate
+    // cost more than the few candidates that no lane takes.
+    auto consider = [&](const double4 &c, double b2, int ent, bool mine) -> bool {
         const double dx = c.x - me.x, dy = c.y - me.y, dz = c.z - me.z;
         // |d|^2 with FMAs: 1 ulp off the reference's mul/add form (:101-104), which moves an
         // accept/open decision only if border/dist sits within an ulp of THETA
         const double d2 = fma(dz, dz, fma(dy, dy, dx * dx));
-        const bool take = ((M >> lane) & 1u) && (b2 < theta2 * d2) && (ent != (int)k);
-        const unsigned T = __ballot_sync(0xffffffffu, take);
-        if (T) {
-            const double s = bh_inv_r3_times_m(d2 + eps2, take ? c.w : 0.0);
-            ax = fma(dx, s, ax); ay = fma(dy, s, ay); az = fma(dz, s, az);
-        }
+        const bool take = mine & (b2 < theta2 * d2) & (ent != (int)k); // no short circuit
+        const double s0 = bh_inv_r3_times_m(d2 + eps2, c.w);
+        const double s = take ? s0 : 0.0; // selected after the fact: a NaN/inf of a lane that does not take it is dropped
+        ax = fma(dx, s, ax); ay = fma(dy, s, ay); az = fma(dz, s, az);
         if (COUNT) {
             n_inter += take;
-            n_visit += ent >= 0 ? take : (M >> lane) & 1u; // the body's own leaf is never visited
+            n_visit += ent >= 0 ? take : mine; // the body's own leaf is never visited
         }
-        return T;
+        return take;
     };
 
     if (all && a.p.n >= 2) { // a single body feels nothing (the root needs >= 2 bodies)
         // the root is tested like any cell (:405)
-        const unsigned O = all & ~consider(com[0], s_border2[0], -2, all);
+        const bool took = consider(com[0], s_border2[0], -2, valid);
+        const unsigned O = __ballot_sync(0xffffffffu, valid && !took);
         if (O) {
-            if (lane == 0) stk[0] = make_uint2(0u, O); // id 0, depth 0
+            stk[0] = make_uint2(a.flags[3], O);
             sp = 1;
         }
     }
@@ -373,49 +395,52 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
     while (sp > 0) {
         --sp;
         const uint2 top = stk[sp];
-        const unsigned nd = top.x & 0x07ffffffu, lvl = top.x >> 27, M = top.y;
-        if (lvl == BH_MAX_LEVEL) { // bucket: bodies sharing one finest cell, summed directly
+        const unsigned nd = top.x & BH_CODE_ID, M = top.y;
+        const bool mine = (M >> lane) & 1u;
+        if (top.x & BH_CODE_BUCKET) { // bodies sharing one finest cell, summed directly
             const unsigned f = a.first[nd], cn = a.count[nd];
             for (unsigned t = f; t < f + cn; ++t) {
-                consider(spos[t], -1.0, (int)t, M);
-                if (COUNT) n_visit -= (M >> lane) & 1u && t != k; // members are not tree nodes
+                consider(spos[t], -1.0, (int)t, mine);
+                if (COUNT) n_visit -= mine && t != k; // members are not tree nodes
             }
             continue;
         }
-        // The node's child records are one 512-byte block: lanes 0..7 fetch one record each
-        // (one coalesced round trip per opened cell) and stage them in shared memory, from
-        // where all lanes read them as broadcasts.  Cells that some lane must open go to the
-        // stack; walking the list backwards leaves the first child on top, so it is walked
-        // first (the reference's depth-first order).
-        const ChildRec *blk = cblock + (size_t)nd * 8;
-        int ent_l = 0;
-        if (lane < 8) {
-            const double4 cc = blk[lane].c;
-            const double2 be = *reinterpret_cast<const double2 *>(&blk[lane].b2); // b2 | ent, pad
-            slot[lane].c = cc;
-            *reinterpret_cast<double2 *>(&slot[lane].b2) = be;
-            ent_l = __double2loint(be.y);
-        }
-        // the list ends at the first record with ent == -1 (what follows it is stale)
-        const unsigned endm = __ballot_sync(0xffffffffu, ent_l == -1);
-        const int nc = endm ? __ffs(endm) - 1 : 8;
+        // The node's child records are one 512-byte block: the 32 lanes copy 16 bytes each
+        // (one coalesced round trip per opened cell) into shared memory, from where all lanes
+        // read the records as broadcasts.  How many records count is in the stack word.  Two
+        // buffers alternate, so one barrier per cell orders everything: a lane that runs ahead
+        // into the next cell writes the other buffer, and cannot pass that cell's barrier
+        // before every lane has left this one.
+        const int nc = (int)((top.x >> BH_CODE_NC_SHIFT) & 7u) + 1;
+        ChildRec *slot = s_child[warp][flip];
+        flip ^= 1;
+        reinterpret_cast<uint4 *>(slot)[lane] =
+            reinterpret_cast<const uint4 *>(cblock + (size_t)nd * 8)[lane];
         if (sp + nc > TRAV_STACK) { // cannot happen for depth <= BH_MAX_LEVEL; flagged, not silent
             if (lane == 0) a.flags[1] = 1;
             break;
         }
         __syncwarp();
+        // Children last to first; a lane notes in `open` (bit c) the candidates it did not take:
+        // cells it must descend into (and, once per walk, its own body's leaf).
+        unsigned open = 0;
         for (int c = nc - 1; c >= 0; --c) {
             const double4 cc = slot[c].c;
-            const double b2 = slot[c].b2;
-            const int ent = slot[c].ent;
-            const unsigned T = consider(cc, b2, ent, M);
-            const unsigned O = ent < 0 ? (M & ~T) : 0u;
-            if (O) {
-                if (lane == 0) stk[sp] = make_uint2((unsigned)(-ent - 2) | ((lvl + 1u) << 27), O);
-                ++sp;
-            }
+            const double2 be = *reinterpret_cast<const double2 *>(&slot[c].b2); // b2 | ent, code
+            const bool took = consider(cc, be.x, __double2loint(be.y), mine);
+            open = open * 2u + (unsigned)(mine & !took);
         }
-        __syncwarp();
+        // Cells that some lane must open go to the stack, last child first, so the first child
+        // ends on top and is walked first (the reference's depth-first order).  Every lane
+        // stores the same words, so each lane's later pop reads them whatever the lanes' order.
+        unsigned todo = __reduce_or_sync(0xffffffffu, open);
+        while (todo) {
+            const int c = 31 - __clz(todo);
+            todo &= ~(1u << c);
+            const int2 ec = *reinterpret_cast<const int2 *>(&slot[c].ent); // ent, code
+            if (ec.x >= 0) continue; // a lane's own body
+            stk[sp++] = make_uint2((unsigned)ec.y, __ballot_sync(0xffffffffu, (open >> c) & 1u));
+        }
     }
 
     if (COUNT && a.counters) {

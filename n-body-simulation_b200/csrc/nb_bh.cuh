@@ -21,9 +21,13 @@ constexpr int BH_MAX_LEVEL = 21; // 3 x 21 = 63 key bits; deeper cells become bu
 struct __align__(32) ChildRec {
     double4 c;  // body: x,y,z,m; cell: centre of mass + mass
     double b2;  // cell: border^2 at its depth; body: -1 (always "far enough")
-    int ent;    // >= 0 body (sorted index), <= -2 cell -(id + 2), -1 end of list
-    int pad[5];
+    int ent;    // >= 0 body (sorted index), <= -2 cell -(id + 2)
+    int code;   // cell: what the walk pushes to open it -- id | (children - 1) << 27 | bucket << 30
+    int pad[4];
 };
+constexpr unsigned BH_CODE_ID = 0x07ffffffu; // 27 bits of node id
+constexpr int BH_CODE_NC_SHIFT = 27;         // 3 bits: non-empty children - 1
+constexpr unsigned BH_CODE_BUCKET = 1u << 30; // a finest-level cell: bodies summed directly
 
 // Device buffers of one engine's tree.  Bodies are referred to by their rank k
 // in Morton order ("sorted index"); perm[k] is the body's index in the state
@@ -49,7 +53,7 @@ struct BhTree {
     unsigned *pslot = nullptr;         // node -> index of its record in the parent's block
     // bookkeeping (device)
     unsigned *level_count = nullptr; // [BH_MAX_LEVEL + 2] nodes per level
-    unsigned *flags = nullptr;       // [0] node-pool overflow, [1] stack overflow, [2] own count
+    unsigned *flags = nullptr;       // [0] node-pool overflow, [1] stack overflow, [2] own count, [3] root code
     double *bbox = nullptr;          // [0] max |coord| (as ordered bits during the reduction)
     // radix-sort scratch
     unsigned *hist = nullptr; // [256][sort_blocks]
