@@ -132,6 +132,24 @@ def test_bh_coincident_bodies_bucket(nb):
     assert err.max() <= 1.2e-1 and np.median(err) <= 1e-2
 
 
+def test_bh_node_pool_exhaustion_is_an_error(nb):
+    """Tight pairs spread over the box need a chain of single-child cells each, down to the
+    finest level: far more cells than the pool (2n + 4096) holds.  The reference prints
+    "Too many nodes" and exits (openmp/barnes-hut.c:158-161); the engine finishes the walk on
+    a truncated tree without touching invalid memory and refuses to hand out the result."""
+    rng = np.random.default_rng(23)
+    half = 4000
+    a = rng.uniform(-1, 1, (half, 3))
+    pm = np.concatenate([np.concatenate([a, a + 1e-8]), np.ones((2 * half, 1))], axis=1)
+    vel = np.zeros((2 * half, 3))
+    with bh_engine(nb, pm, vel) as e:
+        with pytest.raises(nb.NbodyError) as ei:
+            e.accelerations()
+            e.gather()
+        assert ei.value.code == -3             # NB_E_NOMEM
+        assert "pool" in str(ei.value)
+
+
 def test_bh_fp32_is_refused(nb):
     g = golden("10_bodies")
     with pytest.raises(nb.NbodyError) as ei:
