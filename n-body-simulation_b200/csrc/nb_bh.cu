@@ -304,7 +304,6 @@ struct TravArgs {
     const double4 *spos, *com;
     const ChildRec *cblock;
     const unsigned *first, *count, *perm, *own;
-    const unsigned char *level;
     const double *bbox;
     unsigned *flags;
     unsigned long long *counters;
@@ -333,13 +332,6 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
 {
     __shared__ uint2 s_stack[TRAV_WARPS][TRAV_STACK]; // {cell id | depth << 27, lanes that must open it}
     __shared__ ChildRec s_child[TRAV_WARPS][2][8];
-    __shared__ double s_border2[BH_MAX_LEVEL + 2];
-    if (threadIdx.x <= BH_MAX_LEVEL) {
-        double b = 2.0 * a.bbox[0]; // root border = max (serial/barnes-hut.c:470), halved per level
-        for (unsigned l = 0; l < threadIdx.x; ++l) b /= 2;
-        s_border2[threadIdx.x] = b * b;
-    }
-    __syncthreads();
 
     // pointers and scalars in registers: the walk below is issue-bound, not FP64-bound
     const double4 *__restrict__ spos = a.spos;
@@ -383,8 +375,10 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
     };
 
     if (all && a.p.n >= 2) { // a single body feels nothing (the root needs >= 2 bodies)
+        const double root_border = 2.0 * a.bbox[0]; // = max (serial/barnes-hut.c:470)
+        const double root_b2 = root_border * root_border;
         // the root is tested like any cell (:405)
-        const bool took = consider(com[0], s_border2[0], -2, valid);
+        const bool took = consider(com[0], root_b2, -2, valid);
         const unsigned O = __ballot_sync(0xffffffffu, valid && !took);
         if (O) {
             stk[0] = make_uint2(a.flags[3], O);
@@ -593,7 +587,7 @@ cudaError_t bh_evaluate(BhTree *t, const BhParams &p, cudaStream_t s, unsigned *
     ta.spos = t->spos; ta.com = t->com; ta.cblock = t->cblock;
     ta.first = t->first; ta.count = t->count; ta.perm = t->val[0];
     ta.own = sliced ? t->own : nullptr;
-    ta.level = t->level; ta.bbox = t->bbox; ta.flags = t->flags; ta.counters = t->counters;
+    ta.bbox = t->bbox; ta.flags = t->flags; ta.counters = t->counters;
     ta.n_own_static = n;
     ta.p = p;
     const unsigned max_own = sliced ? (p.own_end > p.own_begin ? min(p.own_end, n) - min(p.own_begin, n) : 0u) : n;
