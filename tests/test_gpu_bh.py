@@ -157,10 +157,13 @@ def test_bh_fp32_is_refused(nb):
     assert ei.value.code == -1
 
 
-def test_bh_large_n_envelope(nb):
-    """200k bodies: Barnes-Hut against the direct-sum kernel on the same positions."""
+@pytest.mark.parametrize("n", [200_000, 1_000_000])   # 1M: BASELINE config 4
+def test_bh_large_n_envelope(nb, n):
+    """Barnes-Hut against the direct-sum kernel on the same positions (the "direct-sum accuracy
+    check" of BASELINE config 4), plus two properties that need no reference: THETA = 0 opens
+    every cell, so a sample of bodies must reproduce the direct sum to rounding; and the counted
+    interactions of two engines on the same input agree exactly (deterministic lists)."""
     rng = np.random.default_rng(17)
-    n = 200_000
     pm = np.concatenate([rng.standard_normal((n, 3)), np.full((n, 1), 1.0 / n)], axis=1)
     vel = np.zeros((n, 3))
     with nb.Engine(pm, vel, precision=nb.PREC_FP64) as e:
@@ -172,3 +175,11 @@ def test_bh_large_n_envelope(nb):
     assert np.median(err) <= 4e-3 and np.percentile(err, 99) <= 2e-2 and err.max() <= 1.2e-1
     assert 0.3 * n < ti.nodes < 1.0 * n          # the reference measures ~0.49 N internal cells
     assert 500 < ti.interactions / n < 5000
+    with bh_engine(nb, pm, vel, tune_flags=nb.TUNE_COUNT_VISITS) as e:
+        acc_again = e.accelerations()
+        ti2 = e.tree_stats()
+    assert np.array_equal(acc_again, acc) and ti2.interactions == ti.interactions
+    if n <= 200_000:                             # THETA = 0 is the O(N^2) walk: keep it small
+        with bh_engine(nb, pm, vel, theta=0.0) as e:
+            exact = e.accelerations()
+        assert rel_err(exact, ref).max() <= 1e-10

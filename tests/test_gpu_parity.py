@@ -214,14 +214,18 @@ def test_all_size_classes(nb, variant, prec):
 
 
 # -------------------------------------------- size-independent properties ---
-@pytest.mark.parametrize("prec,n", [("fp32", 200_000), ("fp64", 60_000)])
-def test_large_n_properties(nb, prec, n):
-    """At sizes the CPU oracle cannot reach in seconds: (1) Newton's third law --
-    sum_i m_i a_i vanishes to rounding; (2) scaling every mass by 2 doubles every
-    acceleration bit-exactly; (3) a random sample of rows against the oracle."""
+@pytest.mark.parametrize("prec,n,masses", [("fp32", 200_000, "spread"), ("fp64", 60_000, "spread"),
+                                           ("fp32", 1_000_000, "equal"),    # BASELINE config 3 (bench)
+                                           ("fp32", 1_000_000, "spread"),
+                                           ("fp64", 100_000, "equal")])     # BASELINE config 2
+def test_large_n_properties(nb, prec, n, masses):
+    """At sizes the CPU oracle cannot reach in seconds, up to BASELINE.json's full sizes:
+    (1) Newton's third law -- sum_i m_i a_i vanishes to rounding; (2) scaling every mass by 2
+    doubles every acceleration bit-exactly; (3) a random sample of rows against the oracle."""
     import oracle as O
     rng = np.random.default_rng(17)
-    pm = np.concatenate([rng.standard_normal((n, 3)), rng.uniform(0.5, 1.5, (n, 1)) / n], axis=1)
+    m = rng.uniform(0.5, 1.5, (n, 1)) / n if masses == "spread" else np.full((n, 1), 1.0 / n)
+    pm = np.concatenate([rng.standard_normal((n, 3)), m], axis=1)
     if prec == "fp32":
         pm = pm.astype(np.float32).astype(np.float64)
     P = nb.PREC_FP64 if prec == "fp64" else nb.PREC_FP32
