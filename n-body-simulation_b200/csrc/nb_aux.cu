@@ -63,24 +63,35 @@ __global__ void pack_f64_kernel(const double *__restrict__ pos, const double *__
 
 // planes = 4: positions+mass -> out[4b..]; planes = 3: vel / acc -> out[3b..]
 __global__ void unpack_f32_kernel(const float4 *__restrict__ src, unsigned n, int planes,
-                                  double *__restrict__ out)
+                                  double *__restrict__ out, const unsigned *__restrict__ scatter)
 {
     const unsigned b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= n) return;
     const float *f = reinterpret_cast<const float *>(src) + (size_t)(b >> 2) * (planes * 4) + (b & 3);
-    for (int k = 0; k < planes; ++k) out[(size_t)planes * b + k] = (double)f[k * 4];
+    const size_t row = scatter ? scatter[b] : b;
+    for (int k = 0; k < planes; ++k) out[(size_t)planes * row + k] = (double)f[k * 4];
 }
 
 __global__ void unpack_f64_kernel(const double4 *__restrict__ src, unsigned n, int planes,
-                                  double *__restrict__ out)
+                                  double *__restrict__ out, const unsigned *__restrict__ scatter)
 {
     const unsigned b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= n) return;
     const double4 p = src[b];
-    out[(size_t)planes * b + 0] = p.x;
-    out[(size_t)planes * b + 1] = p.y;
-    out[(size_t)planes * b + 2] = p.z;
-    if (planes == 4) out[(size_t)planes * b + 3] = p.w;
+    const size_t row = scatter ? scatter[b] : b;
+    out[(size_t)planes * row + 0] = p.x;
+    out[(size_t)planes * row + 1] = p.y;
+    out[(size_t)planes * row + 2] = p.z;
+    if (planes == 4) out[(size_t)planes * row + 3] = p.w;
+}
+
+__global__ void permute_rows_kernel(const double *__restrict__ src, double *__restrict__ dst,
+                                    const unsigned *__restrict__ order, unsigned n, int planes)
+{
+    const unsigned k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const size_t from = order[k];
+    for (int c = 0; c < planes; ++c) dst[(size_t)planes * k + c] = src[(size_t)planes * from + c];
 }
 
 __global__ void kickdrift_f32_kernel(const float4 *__restrict__ qc, float4 *__restrict__ qn,
@@ -220,13 +231,21 @@ cudaError_t pack_bodies(int precision, const double *pos, const double *vel, uns
 }
 
 cudaError_t unpack_bodies(int precision, const void *src, unsigned n, int planes, double *out,
-                          cudaStream_t s)
+                          const unsigned *scatter, cudaStream_t s)
 {
     if (n == 0) return cudaSuccess;
     if (precision == 1)
-        unpack_f32_kernel<<<cdiv(n, 256), 256, 0, s>>>((const float4 *)src, n, planes, out);
+        unpack_f32_kernel<<<cdiv(n, 256), 256, 0, s>>>((const float4 *)src, n, planes, out, scatter);
     else
-        unpack_f64_kernel<<<cdiv(n, 256), 256, 0, s>>>((const double4 *)src, n, planes, out);
+        unpack_f64_kernel<<<cdiv(n, 256), 256, 0, s>>>((const double4 *)src, n, planes, out, scatter);
+    return cudaGetLastError();
+}
+
+cudaError_t permute_rows(const double *src, double *dst, const unsigned *order, unsigned n,
+                         int planes, cudaStream_t s)
+{
+    if (n == 0) return cudaSuccess;
+    permute_rows_kernel<<<cdiv(n, 256), 256, 0, s>>>(src, dst, order, n, planes);
     return cudaGetLastError();
 }
 

@@ -10,8 +10,12 @@ namespace nb {
 cudaError_t pack_bodies(int precision, const double *pos, const double *vel, unsigned n,
                         unsigned n_units, void *q0, void *q1, void *v, float pad_pos, cudaStream_t s);
 // device layout -> host packing; planes = 4 (pos+mass) or 3 (vel / acc)
+// scatter (optional): body b of the device order goes to row scatter[b] of `out`
 cudaError_t unpack_bodies(int precision, const void *src, unsigned n, int planes, double *out,
-                          cudaStream_t s);
+                          const unsigned *scatter, cudaStream_t s);
+// dst row k = src row order[k] (rows of `planes` doubles)
+cudaError_t permute_rows(const double *src, double *dst, const unsigned *order, unsigned n,
+                         int planes, cudaStream_t s);
 // v += (a*dt)/2 ; x' = x + v*dt from stored accelerations, units [i_begin, i_end)
 cudaError_t kickdrift(int precision, const void *qc, void *qn, void *vel, const void *acc,
                       unsigned i_begin, unsigned i_end, unsigned n_real, double dt, cudaStream_t s);

@@ -546,6 +546,24 @@ void bh_free(BhTree *t)
     *t = BhTree();
 }
 
+cudaError_t bh_morton_order(BhTree *t, const double4 *pos, unsigned n, unsigned *order,
+                            cudaStream_t s, unsigned *launches)
+{
+    if (n == 0) return cudaSuccess;
+    unsigned nl = 0;
+    const unsigned nblk = (n + BH_THREADS - 1) / BH_THREADS;
+    const unsigned wide = nblk < 148u * 8u ? nblk : 148u * 8u;
+    reset_kernel<<<1, 32, 0, s>>>(t->level_count, t->flags, t->bbox, t->first, t->count, t->level,
+                                  n, t->counters, 0);
+    bbox_kernel<<<wide, BH_THREADS, 0, s>>>(pos, n, reinterpret_cast<unsigned long long *>(t->bbox));
+    morton_kernel<<<nblk, BH_THREADS, 0, s>>>(pos, n, t->bbox, t->key[0], t->val[0]);
+    nl += 3;
+    BH_TRY(bh_radix_sort(t, n, 3 * BH_MAX_LEVEL, s, &nl));
+    BH_TRY(cudaMemcpyAsync(order, t->val[0], (size_t)n * sizeof(unsigned), cudaMemcpyDeviceToDevice, s));
+    if (launches) *launches += nl;
+    return cudaGetLastError();
+}
+
 cudaError_t bh_evaluate(BhTree *t, const BhParams &p, cudaStream_t s, unsigned *launches)
 {
     const unsigned n = p.n;

@@ -81,6 +81,11 @@ void bh_free(BhTree *t);
 // kick/drift epilogue selected by p.flags.  Returns the number of kernel launches
 // through *launches.
 cudaError_t bh_evaluate(BhTree *t, const BhParams &p, cudaStream_t s, unsigned *launches);
+// Morton order of n bodies given as x,y,z,m rows: order[k] = row of the body of rank k
+// (the keys and the sort of bh_evaluate, without the tree).  Used once per upload to lay
+// the state out along the curve, so that rank slices are compact regions of space.
+cudaError_t bh_morton_order(BhTree *t, const double4 *pos, unsigned n, unsigned *order,
+                            cudaStream_t s, unsigned *launches);
 // tree statistics of the last evaluation (host sync): internal nodes, depth,
 // root border, overflow flags
 struct BhStats {

@@ -134,6 +134,11 @@ struct nb_engine {
     unsigned frame_seq = 0;
     DirectPlan plan;
     BhTree tree;            // NB_ALGO_BARNES_HUT only
+    // Barnes-Hut: the device keeps the bodies in the Morton order of the uploaded positions
+    // (rank slices = compact regions, warps of neighbours); user_of[k] = caller's index of
+    // device body k, nullptr = caller's order
+    unsigned *user_of = nullptr;
+    double *order_tmp = nullptr; // 4n doubles of scratch for the reordering
     bool bh = false;
     bool count_visits = false;
     bool uniform = false;   // FP32 direct: all masses equal (as floats) -> mass-free inner loop
@@ -301,6 +306,21 @@ int upload(nb_engine *e, const double *pos, const double *vel)
         e->uniform = same;
         e->uniform_m = (double)m0;
     }
+    if (e->user_of) {
+        // every rank sees all n bodies, so every rank derives the same order
+        unsigned nl = 0;
+        NB_CUDA(bh_morton_order(&e->tree, reinterpret_cast<const double4 *>(e->stage_pos), (unsigned)n,
+                                e->user_of, e->stream, &nl));
+        NB_CUDA(permute_rows(e->stage_pos, e->order_tmp, e->user_of, (unsigned)n, 4, e->stream));
+        NB_CUDA(cudaMemcpyAsync(e->stage_pos, e->order_tmp, n * 4 * sizeof(double),
+                                cudaMemcpyDeviceToDevice, e->stream));
+        if (vel) {
+            NB_CUDA(permute_rows(e->stage_vel, e->order_tmp, e->user_of, (unsigned)n, 3, e->stream));
+            NB_CUDA(cudaMemcpyAsync(e->stage_vel, e->order_tmp, n * 3 * sizeof(double),
+                                    cudaMemcpyDeviceToDevice, e->stream));
+        }
+        e->st.kernel_launches += nl + (vel ? 2 : 1);
+    }
     NB_CUDA(pack_bodies(e->cfg.precision, e->stage_pos, vel ? e->stage_vel : nullptr, (unsigned)n,
                         e->n_units, e->q[0], e->q[1], e->vel, e->uniform ? 1.0e18f : 0.f, e->stream));
     e->st.kernel_launches++;
@@ -378,7 +398,8 @@ void nb_free(nb_engine *e)
     if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
     bh_free(&e->tree);
     void *bufs[] = {e->q[0], e->q[1], e->vel, e->acc, e->workspace, e->partial, e->counters,
-                    e->stage_pos, e->stage_vel, e->energy_part, e->frame_stage[0], e->frame_stage[1]};
+                    e->stage_pos, e->stage_vel, e->energy_part, e->frame_stage[0], e->frame_stage[1],
+                    e->user_of, e->order_tmp};
     if (e->copy_stream) cudaStreamSynchronize(e->copy_stream);
     for (void *b : bufs)
         if (b) cudaFree(b);
@@ -457,6 +478,10 @@ static int init_impl(nb_engine *e, const double *pos, const double *vel)
     e->bh = c.algorithm == NB_ALGO_BARNES_HUT;
     e->count_visits = (c.tune_flags & NB_TUNE_COUNT_VISITS) != 0;
     if (e->bh) NB_CUDA(bh_alloc(&e->tree, (unsigned)e->n));
+    if (e->bh && e->n > 1 && !(c.tune_flags & NB_TUNE_NO_REORDER)) {
+        NB_CUDA(cudaMalloc(&e->user_of, e->n * sizeof(unsigned)));
+        NB_CUDA(cudaMalloc(&e->order_tmp, e->n * 4 * sizeof(double)));
+    }
     NB_CUDA(cudaMalloc(&e->counters, e->plan.counter_bytes ? e->plan.counter_bytes : 16));
     NB_CUDA(cudaMemsetAsync(e->counters, 0, e->plan.counter_bytes ? e->plan.counter_bytes : 16,
                             e->stream));
@@ -605,7 +630,7 @@ int nb_frame_begin(nb_engine *e, double *pos_xyzm)
     const int k = (int)(e->frame_seq++ & 1u);
     // the slot's previous snapshot must have left the device before it is overwritten
     if (e->frame_host[k]) NB_CUDA(cudaStreamWaitEvent(e->stream, e->ev_frame_done[k], 0));
-    NB_CUDA(unpack_bodies(e->cfg.precision, e->q[e->cur], n, 4, e->frame_stage[k], e->stream));
+    NB_CUDA(unpack_bodies(e->cfg.precision, e->q[e->cur], n, 4, e->frame_stage[k], e->user_of, e->stream));
     e->st.kernel_launches++;
     NB_CUDA(cudaEventRecord(e->ev_frame_ready[k], e->stream));
     NB_CUDA(cudaStreamWaitEvent(e->copy_stream, e->ev_frame_ready[k], 0));
@@ -658,7 +683,7 @@ int nb_gather(nb_engine *e, double *pos_xyzm, double *vel_xyz)
         if (rc) return rc;
         rc = ensure_vel_complete(e);
         if (rc) return rc;
-        NB_CUDA(unpack_bodies(e->cfg.precision, e->vel, n, 3, e->stage_vel, e->stream));
+        NB_CUDA(unpack_bodies(e->cfg.precision, e->vel, n, 3, e->stage_vel, e->user_of, e->stream));
         e->st.kernel_launches++;
         if (n)
             NB_CUDA(cudaMemcpyAsync(vel_xyz, e->stage_vel, (size_t)n * 3 * sizeof(double),
@@ -667,7 +692,7 @@ int nb_gather(nb_engine *e, double *pos_xyzm, double *vel_xyz)
     if (pos_xyzm) {
         rc = wait_gather(e);
         if (rc) return rc;
-        NB_CUDA(unpack_bodies(e->cfg.precision, e->q[e->cur], n, 4, e->stage_pos, e->stream));
+        NB_CUDA(unpack_bodies(e->cfg.precision, e->q[e->cur], n, 4, e->stage_pos, e->user_of, e->stream));
         e->st.kernel_launches++;
         if (n)
             NB_CUDA(cudaMemcpyAsync(pos_xyzm, e->stage_pos, (size_t)n * 4 * sizeof(double),
@@ -699,7 +724,7 @@ int nb_accelerations(nb_engine *e, double *acc_xyz)
     rc = wait_gather(e);
     if (rc) return rc;
     const unsigned n = (unsigned)e->n;
-    NB_CUDA(unpack_bodies(e->cfg.precision, e->acc, n, 3, e->stage_vel, e->stream));
+    NB_CUDA(unpack_bodies(e->cfg.precision, e->acc, n, 3, e->stage_vel, e->user_of, e->stream));
     e->st.kernel_launches++;
     if (n)
         NB_CUDA(cudaMemcpyAsync(acc_xyz, e->stage_vel, (size_t)n * 3 * sizeof(double),
@@ -720,8 +745,8 @@ int nb_energy(nb_engine *e, double *KE, double *PE)
     rc = wait_gather(e);
     if (rc) return rc;
     const unsigned n = (unsigned)e->n;
-    NB_CUDA(unpack_bodies(e->cfg.precision, e->vel, n, 3, e->stage_vel, e->stream));
-    NB_CUDA(unpack_bodies(e->cfg.precision, e->q[e->cur], n, 4, e->stage_pos, e->stream));
+    NB_CUDA(unpack_bodies(e->cfg.precision, e->vel, n, 3, e->stage_vel, nullptr, e->stream));
+    NB_CUDA(unpack_bodies(e->cfg.precision, e->q[e->cur], n, 4, e->stage_pos, nullptr, e->stream)); // any order
     NB_CUDA(energy_partials(e->stage_pos, e->stage_vel, n, e->energy_part, e->stream));
     e->st.kernel_launches += 3;
     const unsigned nb = energy_blocks(n);

@@ -183,3 +183,28 @@ def test_bh_large_n_envelope(nb, n):
         with bh_engine(nb, pm, vel, theta=0.0) as e:
             exact = e.accelerations()
         assert rel_err(exact, ref).max() <= 1e-10
+
+
+def test_bh_device_order_is_invisible(nb):
+    """The engine keeps the bodies in Morton order on the device (rank slices = compact regions);
+    every output comes back in the caller's order, bit-identical to an engine that keeps the
+    caller's order (NB_TUNE_NO_REORDER)."""
+    g = golden("1k_bodies")
+    res = []
+    for flags in (0, nb.TUNE_NO_REORDER):
+        with bh_engine(nb, g["pos_xyzm"], g["vel"], tune_flags=flags) as e:
+            acc = e.accelerations()
+            buf = e.frame_buffer()
+            e.step(2)
+            e.frame_begin(buf)
+            e.step(1)
+            e.frame_wait(buf)
+            frame = buf.copy()
+            pos, vel = e.gather()
+            ke, pe = e.energy()
+        res.append((acc, frame, pos, vel, ke, pe))
+    for a, b in zip(res[0][:4], res[1][:4]):
+        assert np.array_equal(a, b)
+    assert np.array_equal(res[0][2][:, 3], g["pos_xyzm"][:, 3])      # masses where the caller put them
+    assert abs(res[0][4] - res[1][4]) <= 1e-12 * abs(res[1][4])      # sums in another order
+    assert abs(res[0][5] - res[1][5]) <= 1e-12 * abs(res[1][5])
