@@ -155,11 +155,19 @@ __global__ void __launch_bounds__(BH_THREADS) build_level_kernel(BuildArgs a, in
     const int oct = threadIdx.x & 7;
     const unsigned gmask = 0xffu << ((threadIdx.x & 31) & ~7); // this node's 8 lanes
     const int shift = 3 * (BH_MAX_LEVEL - 1 - L);
-    const unsigned groups = (gridDim.x * blockDim.x) >> 3;
-    // all 8 lanes of a group run the same trip count
-    for (unsigned g = (blockIdx.x * blockDim.x + threadIdx.x) >> 3; g < cnt; g += groups) {
-        const unsigned nd = base + g;
-        const unsigned f = a.first[nd], c = a.count[nd];
+    // Node ids of the next level come from one counter.  One atomicAdd per node made the
+    // populous levels atomic-bound (3M same-address atomics at 16M bodies); the CTA's 32 nodes
+    // are scanned in shared memory and take their ids with ONE atomicAdd.  Every thread of the
+    // CTA runs the same trip count (idle groups vote with zero children).
+    constexpr unsigned GPC = BH_THREADS / 8; // nodes per CTA and trip
+    __shared__ unsigned s_off[GPC];
+    __shared__ unsigned s_base;
+    const unsigned grp = threadIdx.x >> 3;
+    for (unsigned g0 = blockIdx.x * GPC; g0 < cnt; g0 += gridDim.x * GPC) {
+        const unsigned g = g0 + grp;
+        const bool live = g < cnt;
+        const unsigned nd = base + (live ? g : 0u);
+        const unsigned f = live ? a.first[nd] : 0u, c = live ? a.count[nd] : 0u;
         // lower bound of digit `oct` inside [f, f + c)
         unsigned lo = f, hi = f + c;
         while (lo < hi) {
@@ -173,9 +181,23 @@ __global__ void __launch_bounds__(BH_THREADS) build_level_kernel(BuildArgs a, in
         const unsigned k = end - start;
         const bool branch = k >= 2;
         const unsigned bal = (__ballot_sync(gmask, branch) >> ((threadIdx.x & 31) & ~7)) & 0xffu;
-        unsigned slot = 0;
-        if (oct == 0 && bal) slot = atomicAdd(&a.level_count[L + 1], (unsigned)__popc(bal));
-        slot = __shfl_sync(gmask, slot, 0, 8);
+        if (oct == 0) s_off[grp] = (unsigned)__popc(bal);
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            const unsigned v = s_off[threadIdx.x];
+            unsigned x = v; // inclusive scan over the CTA's 32 nodes
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned y = __shfl_up_sync(0xffffffffu, x, o);
+                if ((int)threadIdx.x >= o) x += y;
+            }
+            if (threadIdx.x == 31 && x) s_base = atomicAdd(&a.level_count[L + 1], x);
+            s_off[threadIdx.x] = x - v;
+        }
+        __syncthreads();
+        const unsigned slot = s_base + s_off[grp]; // s_base is only read when the CTA made nodes
+        __syncthreads(); // the next trip overwrites s_off / s_base
+        if (!live) continue;
         int ch = -1;
         if (k == 1) ch = (int)start;
         else if (branch) {
