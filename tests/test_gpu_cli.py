@@ -124,3 +124,32 @@ def test_barnes_hut_cuda_program(tmp_path, oracle_lib):
     last = f[-100:]
     assert np.array_equal(last[:, 0], np.arange(100))
     assert np.abs(last[:, 1:4] - pm[:, :3]).max() <= 1e-6 and np.abs(last[:, 4] - pm[:, 3]).max() <= 1e-6
+
+
+def test_barnes_hut_cuda_matches_reference_program_100_steps(tmp_path):
+    """tests/golden/programs_bh.npz: the reference's serial/barnes-hut.c (-DRESULTS) on
+    1k_bodies.csv `0 1 0.01`, run in the build container.  Its file starts with the initial
+    frame, which the CUDA program (and ours) leaves out; the 100 frames that follow are compared
+    number by number (one unit of the sixth decimal) and, since the walk reproduces the
+    reference's interaction lists, byte for byte."""
+    ref = golden("programs_bh")
+    inp, out = write_csv(tmp_path, "1k_bodies"), str(tmp_path / "bh.csv")
+    r = run("barnes-hut-cuda", inp, 0, 1, 0.01, out)
+    assert r.returncode == 0, r.stderr
+    assert "time steps: 100, ents: 1000" in r.stdout
+    data = open(out, "rb").read()
+    lines = data.decode().splitlines()
+    assert len(lines) == int(ref["bh_serial_1k_lines"]) - 1000 == 100 * 1000
+    want_last = str(ref["bh_serial_1k_last_frame"]).splitlines()
+    got = np.array([[float(x) for x in ln.split(",")] for ln in lines[-1000:]])
+    want = np.array([[float(x) for x in ln.split(",")] for ln in want_last])
+    assert np.abs(got - want).max() <= 1.0000001e-6
+    assert hashlib.md5(data).hexdigest() == str(ref["bh_serial_1k_steps_md5"])
+
+
+def test_barnes_hut_cuda_five_frames_equal_reference(tmp_path):
+    ref = str(golden("programs_bh")["bh_serial_100_bodies_g1_5steps"]).splitlines()[100:]
+    inp, out = write_csv(tmp_path, "100_bodies_g1"), str(tmp_path / "bh5.csv")
+    r = run("barnes-hut-cuda", inp, 0, 0.05, 0.01, out)
+    assert r.returncode == 0, r.stderr
+    assert open(out).read().splitlines() == ref
