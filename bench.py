@@ -292,7 +292,12 @@ def run_gpu_arm(args):
         per_launch_flops = FLOP_PER_INTERACTION * float(my_rows) * float(st0.n_padded)
         ach = per_launch_flops / (force_ms / args.steps * 1e-3) / 1e12
         roof = {"bound": "fma", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
-                "frac": ach / peak, "traffic": None,
+                "frac": ach / peak,
+                # one ncu --set full capture of this very launch (1M bodies, FP32, one GPU):
+                # dram__bytes_read.sum 29.02 MB + dram__bytes_write.sum 1.65 MB
+                # (profiles/r1_f32_direct_1M_ncu_full.csv); other shapes were not captured
+                "traffic": 30671104 if (n == 1_000_000 and world == 1 and prec == nb.PREC_FP32
+                                        and st0.uniform_mass) else None,
                 "peak_source": "nominal: 148 SM x 128 FP32 lanes x 2 x 1965 MHz "
                                "(MEASURED_PEAKS.json has no FP32 FMA figure; sm_max_mhz from it)",
                 "flop_per_interaction": FLOP_PER_INTERACTION,
@@ -304,8 +309,9 @@ def run_gpu_arm(args):
                                                * SM_MAX_MHZ * 1e6
                                                * FLOP_PER_INTERACTION / 1e12) if prec == nb.PREC_FP32
                 else (SM_COUNT * 62.2 / 16.0 * SM_MAX_MHZ * 1e6 * FLOP_PER_INTERACTION / 1e12),
-                "traffic_note": "ncu dram__bytes_read+write per launch: profiles/ (kernel is FMA-bound, "
-                                "HBM traffic ~1e-4 of the time budget)",
+                "traffic_note": "bytes per launch from ncu (dram read + write); the algorithmic 64 B/body "
+                                "include the 32 MB of writes, which leave L2 only after the launch. "
+                                "The kernel is FMA-bound: HBM traffic is ~1e-4 of the time budget",
                 "hbm_algorithmic_bytes_per_launch": 64.0 * my_rows if prec == nb.PREC_FP32
                 else 128.0 * my_rows}
         if clocks and clocks.get("sm_mhz"):
