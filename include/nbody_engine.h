@@ -71,6 +71,7 @@ typedef struct nb_config {
 #define NB_TUNE_NO_UNIFORM 16  /* FP32: keep m_j in the inner loop even when all masses are equal */
 #define NB_TUNE_COUNT_VISITS 8 /* Barnes-Hut: count interactions / node visits (nb_tree_stats) */
 #define NB_TUNE_NO_REORDER 32  /* Barnes-Hut: keep the caller's body order on the device */
+#define NB_TUNE_NO_INTERLEAVE 64 /* Barnes-Hut, world > 1: rank slices = contiguous pieces of the Morton curve */
 
 typedef struct nb_stats {
     double last_step_ms;        /* device time (CUDA events on the engine stream) of the last nb_step */

@@ -85,6 +85,13 @@ __global__ void unpack_f64_kernel(const double4 *__restrict__ src, unsigned n, i
     if (planes == 4) out[(size_t)planes * row + 3] = p.w;
 }
 
+__global__ void remap_chunks_kernel(const unsigned *__restrict__ in, unsigned *__restrict__ out, unsigned n,
+                                    unsigned chunk, const unsigned *__restrict__ chunk_base)
+{
+    const unsigned m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m < n) out[chunk_base[m / chunk] + m % chunk] = in[m];
+}
+
 __global__ void permute_rows_kernel(const double *__restrict__ src, double *__restrict__ dst,
                                     const unsigned *__restrict__ order, unsigned n, int planes)
 {
@@ -238,6 +245,14 @@ cudaError_t unpack_bodies(int precision, const void *src, unsigned n, int planes
         unpack_f32_kernel<<<cdiv(n, 256), 256, 0, s>>>((const float4 *)src, n, planes, out, scatter);
     else
         unpack_f64_kernel<<<cdiv(n, 256), 256, 0, s>>>((const double4 *)src, n, planes, out, scatter);
+    return cudaGetLastError();
+}
+
+cudaError_t remap_chunks(const unsigned *in, unsigned *out, unsigned n, unsigned chunk,
+                         const unsigned *chunk_base, cudaStream_t s)
+{
+    if (n == 0) return cudaSuccess;
+    remap_chunks_kernel<<<cdiv(n, 256), 256, 0, s>>>(in, out, n, chunk, chunk_base);
     return cudaGetLastError();
 }
 

@@ -16,6 +16,9 @@ cudaError_t unpack_bodies(int precision, const void *src, unsigned n, int planes
 // dst row k = src row order[k] (rows of `planes` doubles)
 cudaError_t permute_rows(const double *src, double *dst, const unsigned *order, unsigned n,
                          int planes, cudaStream_t s);
+// out[chunk_base[m / chunk] + m % chunk] = in[m]: deals chunks of a sequence out to new places
+cudaError_t remap_chunks(const unsigned *in, unsigned *out, unsigned n, unsigned chunk,
+                         const unsigned *chunk_base, cudaStream_t s);
 // v += (a*dt)/2 ; x' = x + v*dt from stored accelerations, units [i_begin, i_end)
 cudaError_t kickdrift(int precision, const void *qc, void *qn, void *vel, const void *acc,
                       unsigned i_begin, unsigned i_end, unsigned n_real, double dt, cudaStream_t s);

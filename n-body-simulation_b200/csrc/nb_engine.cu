@@ -20,6 +20,8 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <algorithm>
+#include <vector>
 
 #include "../../include/nbody_engine.h"
 #include "nb_aux.cuh"
@@ -139,6 +141,7 @@ struct nb_engine {
     // device body k, nullptr = caller's order
     unsigned *user_of = nullptr;
     double *order_tmp = nullptr; // 4n doubles of scratch for the reordering
+    unsigned *morton_tmp = nullptr, *chunk_base = nullptr; // world > 1: dealing the curve out to the ranks
     bool bh = false;
     bool count_visits = false;
     bool uniform = false;   // FP32 direct: all masses equal (as floats) -> mass-free inner loop
@@ -282,6 +285,45 @@ int ensure_vel_complete(nb_engine *e)
     return wait_gather(e);
 }
 
+// World > 1, Barnes-Hut: the ranks' slices are contiguous in the device order, and equal in
+// bodies -- but a contiguous piece of the Morton curve is a region of space, and regions differ in
+// work per body.  So the curve is dealt out in chunks of 128 bodies, round robin: every rank gets
+// every world-th chunk (neighbours stay together inside a chunk = 4 warps of the walk) and so a
+// fair sample of every region.  user_of[device index] = morton_tmp[rank on the curve].
+constexpr unsigned kDealChunk = 128; // = the slice alignment of FP64 engines
+
+int deal_curve(nb_engine *e)
+{
+    const unsigned n = (unsigned)e->n, world = (unsigned)e->cfg.world, len = e->slice_units;
+    const unsigned full = n / kDealChunk, rag = n % kDealChunk;
+    std::vector<unsigned> base(full + 1, 0u), fill(world, 0u), cap(world, 0u);
+    for (unsigned r = 0; r < world; ++r) {
+        const size_t lo = (size_t)r * len;
+        cap[r] = lo >= n ? 0u : (unsigned)std::min<size_t>(len, n - lo);
+    }
+    unsigned r = 0;
+    for (unsigned c = 0; c < full; ++c) {
+        unsigned tries = 0;
+        while (fill[r] + kDealChunk > cap[r] && tries++ < world) r = (r + 1) % world;
+        if (fill[r] + kDealChunk > cap[r]) {
+            set_err("nb_upload", "internal: slice capacities do not add up");
+            return NB_E_INVALID;
+        }
+        base[c] = r * len + fill[r];
+        fill[r] += kDealChunk;
+        r = (r + 1) % world;
+    }
+    if (rag) { // the last, short chunk closes the one slice whose length is not a multiple of 128
+        const unsigned rr = (n - 1) / len;
+        base[full] = rr * len + fill[rr];
+    }
+    NB_CUDA(cudaMemcpyAsync(e->chunk_base, base.data(), base.size() * sizeof(unsigned),
+                            cudaMemcpyHostToDevice, e->stream));
+    NB_CUDA(remap_chunks(e->morton_tmp, e->user_of, n, kDealChunk, e->chunk_base, e->stream));
+    NB_CUDA(cudaStreamSynchronize(e->stream)); // `base` leaves scope
+    return NB_OK;
+}
+
 int upload(nb_engine *e, const double *pos, const double *vel)
 {
     const size_t n = e->n;
@@ -310,7 +352,12 @@ int upload(nb_engine *e, const double *pos, const double *vel)
         // every rank sees all n bodies, so every rank derives the same order
         unsigned nl = 0;
         NB_CUDA(bh_morton_order(&e->tree, reinterpret_cast<const double4 *>(e->stage_pos), (unsigned)n,
-                                e->user_of, e->stream, &nl));
+                                e->morton_tmp ? e->morton_tmp : e->user_of, e->stream, &nl));
+        if (e->morton_tmp) {
+            int rc = deal_curve(e);
+            if (rc) return rc;
+            ++nl;
+        }
         NB_CUDA(permute_rows(e->stage_pos, e->order_tmp, e->user_of, (unsigned)n, 4, e->stream));
         NB_CUDA(cudaMemcpyAsync(e->stage_pos, e->order_tmp, n * 4 * sizeof(double),
                                 cudaMemcpyDeviceToDevice, e->stream));
@@ -399,7 +446,7 @@ void nb_free(nb_engine *e)
     bh_free(&e->tree);
     void *bufs[] = {e->q[0], e->q[1], e->vel, e->acc, e->workspace, e->partial, e->counters,
                     e->stage_pos, e->stage_vel, e->energy_part, e->frame_stage[0], e->frame_stage[1],
-                    e->user_of, e->order_tmp};
+                    e->user_of, e->order_tmp, e->morton_tmp, e->chunk_base};
     if (e->copy_stream) cudaStreamSynchronize(e->copy_stream);
     for (void *b : bufs)
         if (b) cudaFree(b);
@@ -481,6 +528,10 @@ static int init_impl(nb_engine *e, const double *pos, const double *vel)
     if (e->bh && e->n > 1 && !(c.tune_flags & NB_TUNE_NO_REORDER)) {
         NB_CUDA(cudaMalloc(&e->user_of, e->n * sizeof(unsigned)));
         NB_CUDA(cudaMalloc(&e->order_tmp, e->n * 4 * sizeof(double)));
+        if (c.world > 1 && !(c.tune_flags & NB_TUNE_NO_INTERLEAVE)) {
+            NB_CUDA(cudaMalloc(&e->morton_tmp, e->n * sizeof(unsigned)));
+            NB_CUDA(cudaMalloc(&e->chunk_base, (e->n / kDealChunk + 1) * sizeof(unsigned)));
+        }
     }
     NB_CUDA(cudaMalloc(&e->counters, e->plan.counter_bytes ? e->plan.counter_bytes : 16));
     NB_CUDA(cudaMemsetAsync(e->counters, 0, e->plan.counter_bytes ? e->plan.counter_bytes : 16,

@@ -174,3 +174,26 @@ def test_barnes_hut_ranks_bitwise(nb, world):
 
     for acc, p, v in run_ranks(nb, world, fn, g["pos_xyzm"], g["vel"], **kw):
         assert np.array_equal(acc, a1) and np.array_equal(p, p1) and np.array_equal(v, v1)
+
+
+@pytest.mark.parametrize("n", [2, 3, 129, 257, 1000])
+@pytest.mark.parametrize("flags", ["deal", "curve", "caller"])
+def test_barnes_hut_ragged_slices_and_orders(nb, n, flags):
+    """Two ranks, sizes around the 128-body chunks the Morton curve is dealt out in (slices that
+    are partly or wholly padding), and the three device orders: chunks dealt round robin
+    (default), contiguous pieces of the curve, the caller's order.  All equal the 1-rank state."""
+    need(nb, 2)
+    g = golden("10k_bodies_g1")
+    pm, vel = g["pos_xyzm"][:n].copy(), g["vel"][:n].copy()
+    tf = {"deal": 0, "curve": nb.TUNE_NO_INTERLEAVE, "caller": nb.TUNE_NO_REORDER}[flags]
+    kw = dict(precision=nb.PREC_FP64, algorithm=nb.ALGO_BARNES_HUT, dt=g["dt"])
+    with nb.Engine(pm, vel, **kw) as e:
+        e.step(2)
+        p1, v1 = e.gather()
+
+    def fn(e, r):
+        e.step(2)
+        return e.gather()
+
+    for p, v in run_ranks(nb, 2, fn, pm, vel, tune_flags=tf, **kw):
+        assert np.array_equal(p, p1) and np.array_equal(v, v1)
