@@ -247,6 +247,18 @@ __global__ void __launch_bounds__(BH_THREADS) build_level_kernel(BuildArgs a, in
     }
 }
 
+// The reference accepts a cell when border / dist < THETA (serial/barnes-hut.c:405).  With
+// r2 = dist^2 + eps2 -- which the interaction needs anyway -- this is
+//     border^2 / THETA^2 + eps2 < r2,
+// one FP64 compare per candidate instead of add + multiply + compare.  The left side is a
+// property of the cell's level and is stored in its record.  THETA = 0 gives +inf (never
+// accept: the direct sum); bodies carry -1 (always accept).  Like the squared form it can differ
+// from the reference's divide-and-compare only when border/dist is within rounding of THETA.
+__host__ __device__ __forceinline__ double bh_threshold(double border, double theta, double eps2)
+{
+    return (border * border) / (theta * theta) + eps2;
+}
+
 // ----------------------------------------------------------------- COM ----
 // center_of_mass (serial/barnes-hut.c:285-317): children folded in octant
 // order with the reference's incremental weighted mean, written as it writes it
@@ -257,12 +269,14 @@ __global__ void __launch_bounds__(BH_THREADS)
                      const unsigned *__restrict__ first, const unsigned *__restrict__ count,
                      const unsigned *__restrict__ level_count, double4 *__restrict__ com, int L,
                      unsigned node_cap, const double *__restrict__ bbox,
-                     ChildRec *__restrict__ cblock, const unsigned *__restrict__ pslot)
+                     ChildRec *__restrict__ cblock, const unsigned *__restrict__ pslot,
+                     double theta, double eps2)
 {
-    // border^2 at depth L: (max / 2^L)^2, the halvings are exact
+    // border^2 at depth L: (max / 2^L)^2, the halvings are exact.  The record carries the
+    // acceptance threshold in the form the walk tests it (bh_threshold).
     double border = 2.0 * bbox[0];
     for (int l = 0; l < L; ++l) border /= 2;
-    const double b2 = border * border;
+    const double b2 = bh_threshold(border, theta, eps2);
     const unsigned base = level_base(level_count, L);
     const unsigned cnt = level_nodes(level_count, L, base, node_cap);
     for (unsigned g = blockIdx.x * blockDim.x + threadIdx.x; g < cnt; g += gridDim.x * blockDim.x) {
@@ -365,7 +379,7 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
     const bool valid = j < n_own;
     const unsigned k = valid ? (a.own ? a.own[j] : j) : 0u;
     const double4 me = spos[k];
-    const double theta2 = a.p.theta * a.p.theta, eps2 = a.p.eps2;
+    const double eps2 = a.p.eps2;
     double ax = 0, ay = 0, az = 0;
     unsigned n_inter = 0, n_visit = 0;
     uint2 *stk = s_stack[warp];
@@ -380,13 +394,13 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
     // it.  Straight-line code: the interaction is computed by every lane and added under a
     // predicate -- the walk is bound by issue slots, and a vote plus a branch per candidate
     // cost more than the few candidates that no lane takes.
-    auto consider = [&](const double4 &c, double b2, int ent, bool mine) -> bool {
+    auto consider = [&](const double4 &c, double thr, int ent, bool mine) -> bool {
         const double dx = c.x - me.x, dy = c.y - me.y, dz = c.z - me.z;
-        // |d|^2 with FMAs: 1 ulp off the reference's mul/add form (:101-104), which moves an
-        // accept/open decision only if border/dist sits within an ulp of THETA
-        const double d2 = fma(dz, dz, fma(dy, dy, dx * dx));
-        const bool take = mine & (b2 < theta2 * d2) & (ent != (int)k); // no short circuit
-        const double s0 = bh_inv_r3_times_m(d2 + eps2, c.w);
+        // dist^2 + eps2 in one FMA chain: within rounding of the reference's mul/add form
+        // (:101-104, :172), which moves an accept/open decision only at the very edge of THETA
+        const double r2 = fma(dz, dz, fma(dy, dy, fma(dx, dx, eps2)));
+        const bool take = mine & (thr < r2) & (ent != (int)k); // no short circuit
+        const double s0 = bh_inv_r3_times_m(r2, c.w);
         const double s = take ? s0 : 0.0; // selected after the fact: a NaN/inf of a lane that does not take it is dropped
         ax = fma(dx, s, ax); ay = fma(dy, s, ay); az = fma(dz, s, az);
         if (COUNT) {
@@ -620,7 +634,7 @@ cudaError_t bh_evaluate(BhTree *t, const BhParams &p, cudaStream_t s, unsigned *
         for (int L = BH_MAX_LEVEL; L >= 0; --L)
             com_level_kernel<<<cgrid, BH_THREADS, 0, s>>>(t->spos, t->child, t->first, t->count,
                                                           t->level_count, t->com, L, t->node_cap, t->bbox,
-                                                          t->cblock, t->pslot);
+                                                          t->cblock, t->pslot, p.theta, p.eps2);
         nl += 2 * BH_MAX_LEVEL + 1;
     }
     TravArgs ta;

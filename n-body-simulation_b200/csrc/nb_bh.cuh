@@ -20,7 +20,7 @@ constexpr int BH_MAX_LEVEL = 21; // 3 x 21 = 63 key bits; deeper cells become bu
 // A child as the traversal sees it (64 bytes, 2 per 128-byte line).
 struct __align__(32) ChildRec {
     double4 c;  // body: x,y,z,m; cell: centre of mass + mass
-    double b2;  // cell: border^2 at its depth; body: -1 (always "far enough")
+    double b2;  // cell: acceptance threshold border^2 / THETA^2 + eps2 (tested against dist^2 + eps2); body: -1
     int ent;    // >= 0 body (sorted index), <= -2 cell -(id + 2)
     int code;   // cell: what the walk pushes to open it -- id | (children - 1) << 27 | bucket << 30
     int pad[4];
