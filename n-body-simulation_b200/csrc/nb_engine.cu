@@ -287,10 +287,14 @@ int ensure_vel_complete(nb_engine *e)
 
 // World > 1, Barnes-Hut: the ranks' slices are contiguous in the device order, and equal in
 // bodies -- but a contiguous piece of the Morton curve is a region of space, and regions differ in
-// work per body.  So the curve is dealt out in chunks of 128 bodies, round robin: every rank gets
-// every world-th chunk (neighbours stay together inside a chunk = 4 warps of the walk) and so a
-// fair sample of every region.  user_of[device index] = morton_tmp[rank on the curve].
+// work per body.  So the curve is dealt out in pieces, round robin: every rank gets every
+// world-th piece and so a sample of every region.  Pieces are runs of 128-body chunks (the slice
+// alignment); kDealPieces of them per rank: long enough that a rank's walks stay in a few
+// subtrees (128-body pieces cost 13 % on 8 GPUs -- every rank then drags the whole deep tree
+// through its L2), short enough to even out a lopsided system.
+// user_of[device index] = morton_tmp[rank on the curve].
 constexpr unsigned kDealChunk = 128; // = the slice alignment of FP64 engines
+constexpr unsigned kDealPieces = 32; // pieces per rank (tune_flags bits 16..23: log2 + 1 overrides)
 
 int deal_curve(nb_engine *e)
 {
@@ -301,17 +305,27 @@ int deal_curve(nb_engine *e)
         const size_t lo = (size_t)r * len;
         cap[r] = lo >= n ? 0u : (unsigned)std::min<size_t>(len, n - lo);
     }
-    unsigned r = 0;
+    const unsigned lg = ((unsigned)e->cfg.tune_flags >> 16) & 0xffu;
+    const unsigned pieces = lg ? 1u << (lg - 1) : kDealPieces;
+    const unsigned run = std::max(1u, len / kDealChunk / pieces); // chunks per piece
+    unsigned r = 0, in_run = 0;
     for (unsigned c = 0; c < full; ++c) {
+        if (in_run == run) { // piece complete: next rank
+            r = (r + 1) % world;
+            in_run = 0;
+        }
         unsigned tries = 0;
-        while (fill[r] + kDealChunk > cap[r] && tries++ < world) r = (r + 1) % world;
+        while (fill[r] + kDealChunk > cap[r] && tries++ < world) { // this slice is full
+            r = (r + 1) % world;
+            in_run = 0;
+        }
         if (fill[r] + kDealChunk > cap[r]) {
             set_err("nb_upload", "internal: slice capacities do not add up");
             return NB_E_INVALID;
         }
         base[c] = r * len + fill[r];
         fill[r] += kDealChunk;
-        r = (r + 1) % world;
+        ++in_run;
     }
     if (rag) { // the last, short chunk closes the one slice whose length is not a multiple of 128
         const unsigned rr = (n - 1) / len;
