@@ -72,6 +72,7 @@ typedef struct nb_config {
 #define NB_TUNE_COUNT_VISITS 8 /* Barnes-Hut: count interactions / node visits (nb_tree_stats) */
 #define NB_TUNE_NO_REORDER 32  /* Barnes-Hut: keep the caller's body order on the device */
 #define NB_TUNE_NO_INTERLEAVE 64 /* Barnes-Hut, world > 1: rank slices = contiguous pieces of the Morton curve */
+#define NB_TUNE_NO_GRAPH 128   /* Barnes-Hut: launch the ~75 kernels of an evaluation one by one, not as a CUDA graph */
 /* bits 8..15: force a kernel size class (value - 1); bits 16..23: Barnes-Hut, world > 1: log2 of the
  * pieces per rank the Morton curve is dealt in, + 1 (0 = the default, 32 pieces) */
 

@@ -142,6 +142,16 @@ struct nb_engine {
     unsigned *user_of = nullptr;
     double *order_tmp = nullptr; // 4n doubles of scratch for the reordering
     unsigned *morton_tmp = nullptr, *chunk_base = nullptr; // world > 1: dealing the curve out to the ranks
+    // A Barnes-Hut evaluation is ~75 short launches with fixed arguments per (ping-pong side,
+    // epilogue flags): captured once as a CUDA graph, replayed afterwards.
+    struct BhGraph {
+        int cur;
+        unsigned flags;
+        cudaGraphExec_t exec;
+        unsigned launches;
+    };
+    std::vector<BhGraph> bh_graphs;
+    bool bh_graphs_off = false;
     bool bh = false;
     bool count_visits = false;
     bool uniform = false;   // FP32 direct: all masses equal (as floats) -> mass-free inner loop
@@ -237,7 +247,40 @@ int launch_force(nb_engine *e, unsigned flags)
         bp.dt = p.dt; bp.eps2 = p.eps2; bp.G = p.G; bp.theta = e->cfg.theta;
         bp.count_visits = e->count_visits ? 1 : 0;
         unsigned nl = 0;
-        NB_CUDA(bh_evaluate(&e->tree, bp, e->stream, &nl));
+        bool done = false;
+        if (!e->bh_graphs_off) {
+            for (const nb_engine::BhGraph &g : e->bh_graphs)
+                if (g.cur == e->cur && g.flags == flags) {
+                    NB_CUDA(cudaGraphLaunch(g.exec, e->stream));
+                    nl = g.launches;
+                    done = true;
+                    break;
+                }
+            if (!done) {
+                // thread-local capture: other engines of this process (one host thread each)
+                // keep allocating and launching meanwhile
+                cudaGraph_t graph = nullptr;
+                cudaGraphExec_t exec = nullptr;
+                cudaError_t ce = cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal);
+                if (ce == cudaSuccess) {
+                    ce = bh_evaluate(&e->tree, bp, e->stream, &nl);
+                    const cudaError_t ee = cudaStreamEndCapture(e->stream, &graph);
+                    if (ce == cudaSuccess) ce = ee;
+                }
+                if (ce == cudaSuccess) ce = cudaGraphInstantiate(&exec, graph, 0);
+                if (graph) cudaGraphDestroy(graph);
+                if (ce == cudaSuccess) {
+                    e->bh_graphs.push_back({e->cur, flags, exec, nl});
+                    NB_CUDA(cudaGraphLaunch(exec, e->stream));
+                    done = true;
+                } else { // no graphs on this engine: fall back to plain launches, loudly in the stats
+                    cudaGetLastError();
+                    e->bh_graphs_off = true;
+                    nl = 0;
+                }
+            }
+        }
+        if (!done) NB_CUDA(bh_evaluate(&e->tree, bp, e->stream, &nl));
         e->st.kernel_launches += nl;
     } else if (e->gather_pending && e->plan.can_split && !(e->cfg.tune_flags & NB_TUNE_NO_OVERLAP)) {
         // positions of the other ranks are still in flight: start on the own slice
@@ -458,6 +501,7 @@ void nb_free(nb_engine *e)
     if (e->stream) cudaStreamSynchronize(e->stream);
     if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
     bh_free(&e->tree);
+    for (const nb_engine::BhGraph &g : e->bh_graphs) cudaGraphExecDestroy(g.exec);
     void *bufs[] = {e->q[0], e->q[1], e->vel, e->acc, e->workspace, e->partial, e->counters,
                     e->stage_pos, e->stage_vel, e->energy_part, e->frame_stage[0], e->frame_stage[1],
                     e->user_of, e->order_tmp, e->morton_tmp, e->chunk_base};
@@ -538,6 +582,7 @@ static int init_impl(nb_engine *e, const double *pos, const double *vel)
     if (e->plan.partial_bytes) NB_CUDA(cudaMalloc(&e->partial, e->plan.partial_bytes));
     e->bh = c.algorithm == NB_ALGO_BARNES_HUT;
     e->count_visits = (c.tune_flags & NB_TUNE_COUNT_VISITS) != 0;
+    e->bh_graphs_off = (c.tune_flags & NB_TUNE_NO_GRAPH) != 0;
     if (e->bh) NB_CUDA(bh_alloc(&e->tree, (unsigned)e->n));
     if (e->bh && e->n > 1 && !(c.tune_flags & NB_TUNE_NO_REORDER)) {
         NB_CUDA(cudaMalloc(&e->user_of, e->n * sizeof(unsigned)));

@@ -22,6 +22,7 @@ COMM_ID_BYTES = 128
 TUNE_SCALAR_FP32, TUNE_NO_SPLIT, TUNE_NO_OVERLAP, TUNE_COUNT_VISITS, TUNE_NO_UNIFORM = 1, 2, 4, 8, 16
 TUNE_NO_REORDER = 32
 TUNE_NO_INTERLEAVE = 64
+TUNE_NO_GRAPH = 128
 SLICE_ALIGN = {PREC_FP32: 64, PREC_FP64: 128}  # units; nb_direct.cuh kSliceAlign*
 
 # every symbol include/nbody_engine.h declares

@@ -37,6 +37,8 @@ def run(spec):
             steps = int(o[6:])
         elif o == "nouniform":
             flags |= nb.TUNE_NO_UNIFORM
+        elif o == "nograph":
+            flags |= nb.TUNE_NO_GRAPH
         elif o == "noreorder":
             flags |= nb.TUNE_NO_REORDER
         elif o == "count":
