@@ -22,6 +22,8 @@
  * Optional knobs (environment, so the reference command line is unchanged):
  *   NB_PRECISION=fp64|fp32 (default fp64, the reference's precision)
  *   NB_DEVICE=<ordinal>    NB_CHECKPOINT=<file>: final state in INPUT format
+ *   NB_CHECKPOINT_EVERY=<k>: also every k steps (no-RESULTS runs), written to <file>.tmp and
+ *   renamed, so a restart (`input = <file>`, start_time = the time reached) never sees a torn file
  */
 #include <stdio.h>
 #include <stdlib.h>
@@ -38,6 +40,18 @@ static void die_engine(const char *what, int rc)
     /* cuda_check_error behaviour, cuda/exhaustive.cu:78-84 */
     fprintf(stderr, "Error: %s (%s)\nLine: %s\n", nb_strerror(rc), nb_last_error(), what);
     exit(EXIT_FAILURE);
+}
+
+/* state in INPUT format (%.17g: restarts are bit-exact), via a temporary file and rename() */
+static int write_checkpoint(const char *path, size_t n, const double *pos, const double *vel)
+{
+    char tmp[4096];
+    if (snprintf(tmp, sizeof tmp, "%s.tmp", path) >= (int)sizeof tmp ||
+        nbh_write_bodies(tmp, n, pos, vel) != NBH_OK || rename(tmp, path) != 0) {
+        fprintf(stderr, "Error opening file '%s'\n", path);
+        return -1;
+    }
+    return 0;
 }
 
 int main(int argc, char *argv[])
@@ -135,8 +149,21 @@ int main(int argc, char *argv[])
         nb_host_free(frame[1]);
         fclose(fpt);
     } else {
-        if (n_steps > 0 && (rc = nb_step(eng, n_steps)))
-            die_engine("nb_step", rc);
+        const char *ck = getenv("NB_CHECKPOINT"), *ev = getenv("NB_CHECKPOINT_EVERY");
+        const int every = (ck && ev) ? atoi(ev) : 0;
+        for (int done = 0; done < n_steps;) {
+            const int k = (every > 0 && every < n_steps - done) ? every : n_steps - done;
+            if ((rc = nb_step(eng, k)))
+                die_engine("nb_step", rc);
+            done += k;
+            if (done < n_steps) { /* intermediate checkpoint; the final one is written below */
+                if ((rc = nb_gather(eng, positions, velocities)))
+                    die_engine("nb_gather", rc);
+                if (write_checkpoint(ck, n_ents, positions, velocities) == 0)
+                    fprintf(stderr, "checkpoint after step %d (t = %f): %s\n", done,
+                            (double)(start + (float)done * dt), ck);
+            }
+        }
     }
     /* closing half kick + read-back of the final state */
     if ((rc = nb_gather(eng, positions, velocities)))
@@ -144,8 +171,8 @@ int main(int argc, char *argv[])
     clock_gettime(CLOCK_REALTIME, &e);
 
     env = getenv("NB_CHECKPOINT");
-    if (env && nbh_write_bodies(env, n_ents, positions, velocities) != NBH_OK)
-        fprintf(stderr, "Error opening file '%s'\n", env);
+    if (env)
+        write_checkpoint(env, n_ents, positions, velocities);
 
     printf("Completed. Output file: %s\n", argv[5]);
     double time_spent = (e.tv_sec - s.tv_sec) + (e.tv_nsec - s.tv_nsec) / BILLION;

@@ -153,3 +153,21 @@ def test_barnes_hut_cuda_five_frames_equal_reference(tmp_path):
     r = run("barnes-hut-cuda", inp, 0, 0.05, 0.01, out)
     assert r.returncode == 0, r.stderr
     assert open(out).read().splitlines() == ref
+
+
+def test_periodic_checkpoints_do_not_change_the_run(tmp_path):
+    """NB_CHECKPOINT_EVERY=k: the state is read back (closing the step) and written every k
+    steps; the final state is bit-identical to the uninterrupted run, and a run restarted from
+    an intermediate checkpoint arrives at the same state."""
+    inp = write_csv(tmp_path, "100_bodies_g1")
+    a, b, mid = (str(tmp_path / n) for n in ("a.csv", "b.csv", "mid.csv"))
+    dt = 0.015625
+    assert run("exh_cuda", inp, 0, 7 * dt, dt, "x", env={"NB_CHECKPOINT": a}).returncode == 0
+    r = run("exh_cuda", inp, 0, 7 * dt, dt, "x", env={"NB_CHECKPOINT": b, "NB_CHECKPOINT_EVERY": "3"})
+    assert r.returncode == 0
+    assert r.stderr.count("checkpoint after step") == 2 and "after step 6 (t = 0.093750)" in r.stderr
+    assert open(a).read() == open(b).read() and not os.path.exists(b + ".tmp")
+    # stop at step 3 (what the first intermediate checkpoint held), restart from there
+    assert run("exh_cuda", inp, 0, 3 * dt, dt, "x", env={"NB_CHECKPOINT": mid}).returncode == 0
+    assert run("exh_cuda", mid, 3 * dt, 7 * dt, dt, "x", env={"NB_CHECKPOINT": mid}).returncode == 0
+    assert open(mid).read() == open(a).read()
