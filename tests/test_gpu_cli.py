@@ -171,3 +171,34 @@ def test_periodic_checkpoints_do_not_change_the_run(tmp_path):
     assert run("exh_cuda", inp, 0, 3 * dt, dt, "x", env={"NB_CHECKPOINT": mid}).returncode == 0
     assert run("exh_cuda", mid, 3 * dt, 7 * dt, dt, "x", env={"NB_CHECKPOINT": mid}).returncode == 0
     assert open(mid).read() == open(a).read()
+
+
+def _gpus():
+    from conftest import load_package
+    return load_package().device_count()
+
+
+@pytest.mark.skipif(_gpus() < 2, reason="needs 2 GPUs")
+def test_programs_on_two_gpus(tmp_path):
+    """NB_GPUS=2: one engine per GPU inside the same program (i-slices + all-gather per step).
+    Direct sum: the frame file agrees with the one-GPU run to the sixth decimal and the final
+    state to 1e-12 (own-slice-first summation order); Barnes-Hut: bit for bit."""
+    inp = write_csv(tmp_path, "1k_bodies")
+    o1, o2, c1, c2 = (str(tmp_path / n) for n in ("o1.csv", "o2.csv", "c1.csv", "c2.csv"))
+    r1 = run("exh_cuda_results", inp, 0, 0.2, 0.01, o1, env={"NB_CHECKPOINT": c1})
+    r2 = run("exh_cuda_results", inp, 0, 0.2, 0.01, o2, env={"NB_CHECKPOINT": c2, "NB_GPUS": "2"})
+    assert r1.returncode == 0 and r2.returncode == 0, r2.stderr
+    assert "time steps: 20, ents: 1000" in r2.stdout and "per GPU" in r2.stdout
+    f1, f2 = frames(o1), frames(o2)
+    assert f1.shape == f2.shape == (21 * 1000, 5) and np.abs(f1 - f2).max() <= 1.0000001e-6
+    s1, s2 = np.loadtxt(c1, delimiter=","), np.loadtxt(c2, delimiter=",")
+    assert np.abs(s1 - s2).max() <= 1e-12 * np.abs(s1).max()
+    b1, b2 = str(tmp_path / "b1.csv"), str(tmp_path / "b2.csv")
+    assert run("barnes-hut-cuda", inp, 0, 0.1, 0.01, b1).returncode == 0
+    r = run("barnes-hut-cuda", inp, 0, 0.1, 0.01, b2, env={"NB_GPUS": "2"})
+    assert r.returncode == 0, r.stderr
+    assert open(b1, "rb").read() == open(b2, "rb").read()
+    # periodic checkpoints are collective: every rank reads the state back at the same steps
+    r = run("exh_cuda", inp, 0, 0.07, 0.01, "x", env={"NB_GPUS": "2", "NB_CHECKPOINT": c2,
+                                                         "NB_CHECKPOINT_EVERY": "3"})
+    assert r.returncode == 0 and r.stderr.count("checkpoint after step") == 2
