@@ -22,6 +22,8 @@
  * Optional knobs (environment, so the reference command line is unchanged):
  *   NB_PRECISION=fp64|fp32 (default fp64, the reference's precision)
  *   NB_DEVICE=<ordinal>    NB_CHECKPOINT=<file>: final state in INPUT format
+ *   NB_ENERGY=1: get_energy() of common/get_energy.c:7-47 on the initial and the final state, on
+ *   the GPU, printed to stderr in the format of its test ("KE: %.15f, PE: %.15f", :57)
  *   NB_GPUS=<n>: one engine per GPU (devices NB_DEVICE .. NB_DEVICE+n-1), i-slices + NCCL
  *   all-gather per step; output identical in form, rank 0 writes it
  *   NB_CHECKPOINT_EVERY=<k>: also every k steps (no-RESULTS runs), written to <file>.tmp and
@@ -68,6 +70,17 @@ struct rank {
     int id;
 };
 
+/* every rank calls it (velocities of a multi-GPU run are gathered collectively), rank 0 prints */
+static void report_energy(nb_engine *eng, int lead, const char *when)
+{
+    double ke = 0, pe = 0;
+    int rc = nb_energy(eng, &ke, &pe);
+    if (rc)
+        die_engine("nb_energy", rc);
+    if (lead)
+        fprintf(stderr, "%s KE: %.15f, PE: %.15f\n", when, ke, pe);
+}
+
 /*
  * The time loop of one rank.  Rank 0 owns the files; the other ranks of a multi-GPU run do
  * the same engine calls (nb_step; nb_gather with velocities is collective) into scratch.
@@ -88,6 +101,10 @@ static void *rank_main(void *arg)
     if ((rc = nb_init(&eng, &cfg, n, R->positions, R->velocities)))
         die_engine("nb_init", rc);
     double *pos = R->positions, *vel = R->velocities;
+    const char *en = getenv("NB_ENERGY");
+    const int energy = en && atoi(en) != 0;
+    if (energy)
+        report_energy(eng, lead, "initial");
     if (multi) {
         pthread_barrier_wait(&R->barrier); /* every rank has read the initial state */
         if (!lead) {
@@ -157,6 +174,8 @@ static void *rank_main(void *arg)
     /* closing half kick + read-back of the final state */
     if ((rc = nb_gather(eng, pos, vel)))
         die_engine("nb_gather", rc);
+    if (energy)
+        report_energy(eng, lead, "final");
 
     nb_stats st;
     if (nb_get_stats(eng, &st) == NB_OK) {

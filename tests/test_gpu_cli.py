@@ -202,3 +202,22 @@ def test_programs_on_two_gpus(tmp_path):
     r = run("exh_cuda", inp, 0, 0.07, 0.01, "x", env={"NB_GPUS": "2", "NB_CHECKPOINT": c2,
                                                          "NB_CHECKPOINT_EVERY": "3"})
     assert r.returncode == 0 and r.stderr.count("checkpoint after step") == 2
+
+
+def test_energy_report_matches_get_energy(tmp_path):
+    """NB_ENERGY=1: KE/PE of the initial and final state as common/get_energy.c computes them
+    (golden values from the reference's get_energy on the reference's own trajectories)."""
+    g = golden("1k_bodies")
+    inp = write_csv(tmp_path, "1k_bodies")
+    r = run("exh_cuda", inp, 0, 0.1, 0.01, "x", env={"NB_ENERGY": "1"})
+    assert r.returncode == 0, r.stderr
+    got = {}
+    for ln in r.stderr.splitlines():
+        if " KE: " in ln:
+            when, rest = ln.split(" KE: ")
+            ke, pe = rest.split(", PE: ")
+            got[when] = (float(ke), float(pe))
+    assert abs(got["initial"][0] - float(g["ke_0"])) <= 1e-12 * abs(float(g["ke_0"]))
+    assert abs(got["initial"][1] - float(g["pe_0"])) <= 1e-12 * abs(float(g["pe_0"]))
+    assert abs(got["final"][0] - float(g["ke_10"])) <= 1e-9 * abs(float(g["ke_10"]))
+    assert abs(got["final"][1] - float(g["pe_10"])) <= 1e-9 * abs(float(g["pe_10"]))
