@@ -153,6 +153,11 @@ def test_barnes_hut_cuda_five_frames_equal_reference(tmp_path):
     r = run("barnes-hut-cuda", inp, 0, 0.05, 0.01, out)
     assert r.returncode == 0, r.stderr
     assert open(out).read().splitlines() == ref
+    # README.md:67 of the reference: an optional cache_sz_MB argument; anything else is a usage error
+    r = run("barnes-hut-cuda", inp, 0, 0.05, 0.01, out, 64)
+    assert r.returncode == 0 and open(out).read().splitlines() == ref
+    r = run("barnes-hut-cuda", inp, 0, 0.05)
+    assert r.returncode == 255 and "Usage" in r.stderr      # `return -1`, cuda/barnes-hut.cu:843
 
 
 def test_periodic_checkpoints_do_not_change_the_run(tmp_path):
