@@ -177,3 +177,24 @@ def test_reader_parallel_ranges_equal_serial_rules(nb, tmp_path):
     open(path, "w").write("\n".join(lines) + "\n1,2,3,")
     pos3, _ = nb.read_bodies(path)
     assert np.array_equal(pos3, pos)
+
+
+def test_threaded_frame_writer_equals_serial_formatter(nb, tmp_path):
+    """nbh_write_frame formats 1024-body chunks on OpenMP threads and writes them in body order:
+    the file is byte for byte what the single-pass formatter produces."""
+    h = nb.load_host_library()
+    libc = C.CDLL(None)
+    libc.fopen.restype = C.c_void_p
+    libc.fopen.argtypes = [C.c_char_p, C.c_char_p]
+    libc.fclose.argtypes = [C.c_void_p]
+    rng = np.random.default_rng(9)
+    for n in (0, 1, 1023, 1024, 1025, 40_000):
+        pm = np.ascontiguousarray(np.concatenate([rng.standard_normal((n, 3)) * 100,
+                                                  rng.uniform(0.1, 2, (n, 1))], axis=1))
+        path = str(tmp_path / ("f%d.csv" % n))
+        fp = libc.fopen(path.encode(), b"w")
+        assert fp
+        h.nbh_write_frame.argtypes = [C.c_void_p, C.c_size_t, np.ctypeslib.ndpointer(np.float64, flags="C")]
+        assert h.nbh_write_frame(fp, n, pm) == 0
+        libc.fclose(fp)
+        assert open(path, "rb").read() == nb.format_frame(pm)
