@@ -21,6 +21,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <algorithm>
+#include <mutex>
 #include <vector>
 
 #include "../../include/nbody_engine.h"
@@ -62,9 +63,11 @@ struct NcclApi {
     const char *(*GetErrorString)(int) = nullptr;
 };
 NcclApi g_nccl;
+std::mutex g_nccl_mutex; // engines of one process start on different host threads
 
 int load_nccl()
 {
+    std::lock_guard<std::mutex> guard(g_nccl_mutex);
     if (g_nccl.lib) return NB_OK;
     const char *names[] = {"libnccl.so.2", "libnccl.so"};
     void *h = nullptr;
