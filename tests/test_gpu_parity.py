@@ -76,6 +76,29 @@ def test_fp64_energy_matches_get_energy(nb, name):
     assert abs(pe1 - g["pe_100"]) <= 1e-9 * abs(g["pe_100"])
 
 
+@pytest.mark.parametrize("n", [1, 2, 255, 256, 257, 700, 1300, 5000])
+@pytest.mark.parametrize("prec", ["fp64", "fp32"])
+def test_energy_kernel_tile_pairing(nb, oracle_lib, n, prec):
+    """The energy kernel pairs row tile b with tile (last - b) per CTA: odd and even tile counts,
+    the middle tile done once, ragged last tiles, coincident bodies (r = 0 contributes nothing,
+    common/get_energy.c:33-36)."""
+    import oracle as O
+    rng = np.random.default_rng(n)
+    pm = np.concatenate([rng.standard_normal((n, 3)), rng.uniform(0.5, 2, (n, 1))], axis=1)
+    vel = rng.standard_normal((n, 3))
+    if n >= 256:
+        pm[200, :3] = pm[3, :3]           # a coincident pair inside one tile
+        pm[n - 1, :3] = pm[0, :3]         # and one across the first and the last tile
+    if prec == "fp32":
+        pm, vel = pm.astype(np.float32).astype(np.float64), vel.astype(np.float32).astype(np.float64)
+    P = nb.PREC_FP64 if prec == "fp64" else nb.PREC_FP32
+    with nb.Engine(pm, vel, precision=P, G=0.7) as e:
+        ke, pe = e.energy()
+    oke, ope = O.get_energy(oracle_lib, pm, vel, G=0.7)
+    assert abs(ke - oke) <= 1e-13 * abs(oke)
+    assert abs(pe - ope) <= 1e-12 * max(abs(ope), 1e-300)
+
+
 def test_get_energy_known_answer(nb):
     # common/get_energy.c:49-59, the reference's only known-answer test (G = 0.7)
     vel = np.array([5, 65, 105, -18, 9, -89, -64, 23, 32, 45, 45, 45, -29, -71, -61.0]).reshape(5, 3)
