@@ -316,6 +316,17 @@ def run_gpu_arm(args):
                 else 128.0 * my_rows}
         if clocks and clocks.get("sm_mhz"):
             roof["frac_at_observed_clock"] = ach / (peak * clocks["sm_mhz"] / SM_MAX_MHZ)
+        # the HBM side of the same launch, against the pool's measured copy bandwidth: shows by how
+        # far the kernel is NOT memory-bound (algorithmic bytes / launch time vs MEASURED_PEAKS.json)
+        hbm_peak, hbm_src = 6528.0, "fallback of the profiling recipe"
+        try:
+            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "MEASURED_PEAKS.json")) as f:
+                hbm_peak, hbm_src = float(json.load(f)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"
+        except Exception:
+            pass
+        hbm_ach = roof["hbm_algorithmic_bytes_per_launch"] / (force_ms / args.steps * 1e-3) / 1e9
+        roof["hbm"] = {"achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_ach / hbm_peak,
+                       "peak_source": hbm_src}
         line = {
             "metric": "pairwise interactions/s", "value": value, "unit": "interactions/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
