@@ -17,6 +17,14 @@
  *
  * Threading: one host thread per engine.  nb_step only enqueues work on the
  * engine's stream; nb_gather / nb_sync wait for it.
+ *
+ * Multi-rank engines (cfg.world > 1): nb_init, nb_upload(_slice), nb_step,
+ * nb_gather with velocities, nb_gather_slice, nb_accelerations and nb_energy are
+ * COLLECTIVE -- they enqueue an ncclAllGather, so every rank must call them, in
+ * the same order (host/main_exh.c does, one thread per rank).  A rank that calls
+ * one of them alone blocks for ever in the collective.  nb_gather with
+ * vel_xyz == NULL, nb_frame_begin/wait, nb_get_stats, nb_tree_stats, nb_sync and
+ * nb_free are local.
  */
 #ifndef NBODY_ENGINE_H
 #define NBODY_ENGINE_H
@@ -53,7 +61,10 @@ typedef struct nb_config {
     int algorithm; /* NB_ALGO_* */
     double dt;     /* time step; the host passes (double)strtof(argv[4]) as the reference does
                       (serial/exhaustive.c:43,51; cuda/exhaustive.cu:49,56) */
-    double eps2;   /* softening, reference literal 0.01 (serial/exhaustive.c:172) */
+    double eps2;   /* softening, reference literal 0.01 (serial/exhaustive.c:172).  The direct sum
+                      needs eps2 > 0: it includes the j = i term like the reference (:163) and the
+                      softening is what makes that term exactly 0 (nb_init returns NB_E_INVALID
+                      otherwise).  Barnes-Hut skips the body's own leaf by index and accepts 0. */
     double G;      /* BIG_G = 1.0 (serial/exhaustive.c:24) */
     double theta;  /* THETA = 0.5 (serial/barnes-hut.c:40); Barnes-Hut only */
     int device;    /* CUDA device ordinal this engine (rank) runs on */
@@ -104,6 +115,19 @@ int nb_init(nb_engine **e, const nb_config *cfg, size_t n, const double *pos_xyz
  * step counter: the H2D half of the end-to-end benchmark. */
 int nb_upload(nb_engine *e, const double *pos_xyzm, const double *vel_xyz);
 
+/* Host I/O by slices, for multi-rank runs (no reference counterpart: the reference is single-GPU;
+ * these stand where cuda/exhaustive.cu:125-129 and :153-165 copy everything).  nb_upload and
+ * nb_gather move all n bodies over every rank's PCIe link; here rank r moves only rows
+ * [begin, begin + count) of the caller's order (nb_io_slice: count = ceil(n / world), the last
+ * rank's share clipped) and the ranks exchange the rest over NVLink (ncclAllGather of the staged
+ * rows / of the velocities).  pos_rows = count x 4 doubles (x,y,z,m), vel_rows = count x 3 (may
+ * be NULL like in nb_upload / nb_gather).  Collective when world > 1; with world == 1 they are
+ * nb_upload / nb_gather.  The state after nb_upload_slice is the state after nb_upload of the
+ * concatenated rows, bit for bit. */
+int nb_io_slice(nb_engine *e, size_t *begin, size_t *count);
+int nb_upload_slice(nb_engine *e, const double *pos_rows, const double *vel_rows);
+int nb_gather_slice(nb_engine *e, double *pos_rows, double *vel_rows);
+
 /* Advances n_steps of kick-drift-kick leapfrog: the time loop of propagation()
  * (serial/exhaustive.c:218-250, cuda/exhaustive.cu:135-151).  One fused
  * force+integrate launch per step; a run of n steps followed by nb_gather
@@ -113,7 +137,9 @@ int nb_step(nb_engine *e, int n_steps);
 /* Copies the current state out: what the reference reads back at
  * cuda/exhaustive.cu:153-165 (positions+mass of the current frame) plus the
  * synchronised velocities v_k.  vel_xyz may be NULL (frame output needs
- * positions only).  Blocks until the engine's stream is idle. */
+ * positions only).  Blocks until the engine's stream is idle.  With
+ * velocities it is collective when world > 1 (closing force evaluation +
+ * all-gather of the velocities). */
 int nb_gather(nb_engine *e, double *pos_xyzm, double *vel_xyz);
 
 /* Frame pipeline for the RESULTS loop (serial/exhaustive.c:208-238 writes one
@@ -133,11 +159,13 @@ int nb_host_free(void *p);
 
 /* acceleration() on the current positions (serial/exhaustive.c:155-181,
  * cuda/exhaustive.cu:273-338, or the Barnes-Hut evaluation): acc_xyz[3n].
- * Does not advance the state. */
+ * Does not advance the state.  Collective when world > 1 (all-gathers the
+ * ranks' slices of the accelerations). */
 int nb_accelerations(nb_engine *e, double *acc_xyz);
 
 /* get_energy() of common/get_energy.c:7-47 on the current state, on the GPU
- * (KE, unsoftened PE over i <= j). */
+ * (KE, unsoftened PE over i <= j).  Collective when world > 1 (closes the step
+ * and all-gathers the velocities). */
 int nb_energy(nb_engine *e, double *KE, double *PE);
 
 /* Barnes-Hut engines: facts about the octree of the last force evaluation --
@@ -152,6 +180,12 @@ typedef struct nb_tree_info {
     double root_border;
     unsigned long long interactions, node_visits;
     int pool_overflow, stack_overflow;
+    /* NB_TUNE_COUNT_VISITS: child records tested by a warp of the walk (17 FP64 warp
+     * instructions each: the FP64-pipe work of the traversal) */
+    unsigned long long child_tests;
+    /* NB_TUNE_NO_GRAPH: device time (ms) of the stages of the last evaluation -- cube + keys,
+     * radix sort, bodies in Morton order (+ own list), build, centre of mass, traversal; else 0 */
+    double stage_ms[6];
 } nb_tree_info;
 int nb_tree_stats(nb_engine *e, nb_tree_info *out);
 

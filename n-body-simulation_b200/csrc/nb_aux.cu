@@ -9,12 +9,32 @@
 namespace nb {
 namespace {
 
+// Are all masses equal as floats (and positive)?  cls[0] starts at 1 (mass_class below) and is
+// cleared by any thread that sees a different mass; cls[1] = bits of (float)m_0.  The FP32
+// direct kernel then drops m_j from its inner loop (nb_direct_f32.cu MODE 2).  Runs on the
+// staged host packing, so the host never walks the masses itself.
+__global__ void mass_class_kernel(const double *__restrict__ pos, unsigned n, unsigned *__restrict__ cls)
+{
+    const float m0 = (float)pos[3];
+    bool differ = false;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        differ |= (float)pos[4 * (size_t)i + 3] != m0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        cls[1] = __float_as_uint(m0);
+        differ |= !(m0 > 0.f);
+    }
+    if (__any_sync(0xffffffffu, differ) && (threadIdx.x & 31) == 0) cls[0] = 0u;
+}
+
 __global__ void pack_f32_kernel(const double *__restrict__ pos, const double *__restrict__ vel,
                                 unsigned n, unsigned n_quads, float4 *__restrict__ q0,
-                                float4 *__restrict__ q1, float4 *__restrict__ v, float pad_pos)
+                                float4 *__restrict__ q1, float4 *__restrict__ v,
+                                const unsigned *__restrict__ cls)
 {
     const unsigned iq = blockIdx.x * blockDim.x + threadIdx.x;
     if (iq >= n_quads) return;
+    // equal-mass kernels ignore m_j: their padding is parked where r^-3 underflows to exactly 0
+    const float pad_pos = (cls && cls[0]) ? 1.0e18f : 0.f;
     float c[7][4];
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
@@ -225,12 +245,24 @@ __global__ void __launch_bounds__(ETB)
 inline unsigned cdiv(unsigned a, unsigned b) { return (a + b - 1) / b; }
 } // namespace
 
+cudaError_t mass_class(const double *pos, unsigned n, unsigned *cls, bool enabled, cudaStream_t s)
+{
+    const unsigned init[2] = {enabled && n ? 1u : 0u, 0u};
+    cudaError_t e = cudaMemcpyAsync(cls, init, sizeof(init), cudaMemcpyHostToDevice, s); // pageable: staged at once
+    if (e != cudaSuccess) return e;
+    if (enabled && n) {
+        const unsigned g = cdiv(n, 256) < 1184u ? cdiv(n, 256) : 1184u;
+        mass_class_kernel<<<g, 256, 0, s>>>(pos, n, cls);
+    }
+    return cudaGetLastError();
+}
+
 cudaError_t pack_bodies(int precision, const double *pos, const double *vel, unsigned n,
-                        unsigned n_units, void *q0, void *q1, void *v, float pad_pos, cudaStream_t s)
+                        unsigned n_units, void *q0, void *q1, void *v, const unsigned *cls, cudaStream_t s)
 {
     if (precision == 1)
         pack_f32_kernel<<<cdiv(n_units, 256), 256, 0, s>>>(pos, vel, n, n_units, (float4 *)q0,
-                                                          (float4 *)q1, (float4 *)v, pad_pos);
+                                                          (float4 *)q1, (float4 *)v, cls);
     else
         pack_f64_kernel<<<cdiv(n_units, 256), 256, 0, s>>>(pos, vel, n, n_units, (double4 *)q0,
                                                           (double4 *)q1, (double4 *)v);

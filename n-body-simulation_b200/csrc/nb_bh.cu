@@ -382,6 +382,7 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
     const double eps2 = a.p.eps2;
     double ax = 0, ay = 0, az = 0;
     unsigned n_inter = 0, n_visit = 0;
+    unsigned n_tests = 0; // records this WARP tested (17 FP64 warp instructions each), same in every lane
     uint2 *stk = s_stack[warp];
     int flip = 0;
     int sp = 0;
@@ -412,9 +413,11 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
 
     if (all && a.p.n >= 2) { // a single body feels nothing (the root needs >= 2 bodies)
         const double root_border = 2.0 * a.bbox[0]; // = max (serial/barnes-hut.c:470)
-        const double root_b2 = root_border * root_border;
-        // the root is tested like any cell (:405)
-        const bool took = consider(com[0], root_b2, -2, valid);
+        // the root is tested like any cell (:405, :434): same threshold form as the child
+        // records carry (border^2 / THETA^2 + eps2 against dist^2 + eps2; THETA = 0 -> +inf)
+        const double root_thr = bh_threshold(root_border, a.p.theta, eps2);
+        const bool took = consider(com[0], root_thr, -2, valid);
+        if (COUNT) ++n_tests;
         const unsigned O = __ballot_sync(0xffffffffu, valid && !took);
         if (O) {
             stk[0] = make_uint2(a.flags[3], O);
@@ -433,6 +436,7 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
                 consider(spos[t], -1.0, (int)t, mine);
                 if (COUNT) n_visit -= mine && t != k; // members are not tree nodes
             }
+            if (COUNT) n_tests += cn;
             continue;
         }
         // The node's child records are one 512-byte block: the 32 lanes copy 16 bytes each
@@ -454,6 +458,7 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
         // Children last to first; a lane notes in `open` (bit c) the candidates it did not take:
         // cells it must descend into (and, once per walk, its own body's leaf).
         unsigned open = 0;
+        if (COUNT) n_tests += (unsigned)nc;
         for (int c = nc - 1; c >= 0; --c) {
             const double4 cc = slot[c].c;
             const double2 be = *reinterpret_cast<const double2 *>(&slot[c].b2); // b2 | ent, code
@@ -480,7 +485,11 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
             ni += __shfl_xor_sync(0xffffffffu, ni, o);
             nv += __shfl_xor_sync(0xffffffffu, nv, o);
         }
-        if (lane == 0) { atomicAdd(&a.counters[0], ni); atomicAdd(&a.counters[1], nv); }
+        if (lane == 0) {
+            atomicAdd(&a.counters[0], ni);
+            atomicAdd(&a.counters[1], nv);
+            atomicAdd(&a.counters[2], (unsigned long long)n_tests);
+        }
     }
     if (!valid) return;
 
@@ -520,14 +529,16 @@ __global__ void reset_kernel(unsigned *level_count, unsigned *flags, double *bbo
         count[0] = n;
         level[0] = 0;
         flags[2] = 0;
-        if (reset_counters) counters[0] = counters[1] = 0;
+        if (reset_counters) counters[0] = counters[1] = counters[2] = 0;
     }
 }
 
 } // namespace
 
 // ------------------------------------------------------------------ host ----
-static unsigned bh_node_cap(unsigned n) { return 2u * n + 4096u; } // < 2^27: ids share a word with the depth
+unsigned long long bh_node_cap_of(size_t n) { return 2ull * n + 4096ull; }
+// nb_init refuses n with bh_node_cap_of(n) > BH_CODE_ID: ids share a word with the child count
+static unsigned bh_node_cap(unsigned n) { return (unsigned)bh_node_cap_of(n); }
 
 size_t bh_bytes(unsigned n)
 {
@@ -567,8 +578,9 @@ cudaError_t bh_alloc(BhTree *t, unsigned n)
     BH_TRY(cudaMemset(t->flags, 0, 4 * sizeof(unsigned)));
     BH_TRY(cudaMalloc(&t->bbox, 2 * sizeof(double)));
     BH_TRY(cudaMalloc(&t->hist, ((size_t)256 * t->sort_blocks + 256) * sizeof(unsigned)));
-    BH_TRY(cudaMalloc(&t->counters, 2 * sizeof(unsigned long long)));
-    BH_TRY(cudaMemset(t->counters, 0, 2 * sizeof(unsigned long long)));
+    BH_TRY(cudaMalloc(&t->counters, 4 * sizeof(unsigned long long)));
+    BH_TRY(cudaMemset(t->counters, 0, 4 * sizeof(unsigned long long)));
+    for (int k = 0; k < BH_STAGES + 1; ++k) BH_TRY(cudaEventCreate(&t->ev[k]));
     return cudaSuccess;
 }
 
@@ -579,6 +591,8 @@ void bh_free(BhTree *t)
                     t->counters};
     for (void *b : bufs)
         if (b) cudaFree(b);
+    for (cudaEvent_t ev : t->ev)
+        if (ev) cudaEventDestroy(ev);
     *t = BhTree();
 }
 
@@ -607,12 +621,21 @@ cudaError_t bh_evaluate(BhTree *t, const BhParams &p, cudaStream_t s, unsigned *
     if (n == 0) return cudaSuccess;
     const unsigned nblk = (n + BH_THREADS - 1) / BH_THREADS;
     const unsigned wide = nblk < 148u * 8u ? nblk : 148u * 8u; // grid-stride kernels: 8 CTAs per SM
+    // stage boundaries for nb_tree_stats (plain launches only: not inside a graph capture)
+    int stage = 0;
+    auto mark = [&]() -> cudaError_t {
+        return p.time_stages ? cudaEventRecord(t->ev[stage++], s) : cudaSuccess;
+    };
+    t->stages_timed = false;
+    BH_TRY(mark()); // 0: cube + keys
     reset_kernel<<<1, 32, 0, s>>>(t->level_count, t->flags, t->bbox, t->first, t->count, t->level,
                                   n, t->counters, p.count_visits);
     bbox_kernel<<<wide, BH_THREADS, 0, s>>>(p.q_cur, n, reinterpret_cast<unsigned long long *>(t->bbox));
     morton_kernel<<<nblk, BH_THREADS, 0, s>>>(p.q_cur, n, t->bbox, t->key[0], t->val[0]);
     nl += 3;
+    BH_TRY(mark()); // 1: sort
     BH_TRY(bh_radix_sort(t, n, 3 * BH_MAX_LEVEL, s, &nl));
+    BH_TRY(mark()); // 2: bodies in Morton order + own list
     gather_sorted_kernel<<<nblk, BH_THREADS, 0, s>>>(p.q_cur, t->val[0], n, t->spos);
     ++nl;
     const bool sliced = !(p.own_begin == 0 && p.own_end >= n);
@@ -624,19 +647,24 @@ cudaError_t bh_evaluate(BhTree *t, const BhParams &p, cudaStream_t s, unsigned *
                                                     t->own_counts, t->own);
         nl += 3;
     }
+    BH_TRY(mark()); // 3: build
     if (n >= 2) {
         BuildArgs ba{t->key[0], t->first, t->count, t->level, t->child, t->level_count, t->flags,
                      t->node_cap, t->spos, t->cblock, t->pslot};
         // a level holds at most n/2 nodes, 8 lanes each
         const unsigned bgrid = min(wide, (n / 2 * 8 + BH_THREADS - 1) / BH_THREADS + 1);
         for (int L = 0; L < BH_MAX_LEVEL; ++L) build_level_kernel<<<bgrid, BH_THREADS, 0, s>>>(ba, L);
+        BH_TRY(mark()); // 4: centre of mass
         const unsigned cgrid = min(wide, (n / 2 + BH_THREADS - 1) / BH_THREADS + 1);
         for (int L = BH_MAX_LEVEL; L >= 0; --L)
             com_level_kernel<<<cgrid, BH_THREADS, 0, s>>>(t->spos, t->child, t->first, t->count,
                                                           t->level_count, t->com, L, t->node_cap, t->bbox,
                                                           t->cblock, t->pslot, p.theta, p.eps2);
         nl += 2 * BH_MAX_LEVEL + 1;
+    } else {
+        BH_TRY(mark());
     }
+    BH_TRY(mark()); // 5: traversal
     TravArgs ta;
     ta.spos = t->spos; ta.com = t->com; ta.cblock = t->cblock;
     ta.first = t->first; ta.count = t->count; ta.perm = t->val[0];
@@ -651,6 +679,8 @@ cudaError_t bh_evaluate(BhTree *t, const BhParams &p, cudaStream_t s, unsigned *
         else traverse_kernel<false><<<tgrid, TRAV_WARPS * 32, 0, s>>>(ta);
         ++nl;
     }
+    BH_TRY(mark()); // 6: end
+    t->stages_timed = p.time_stages != 0;
     if (launches) *launches += nl;
     return cudaGetLastError();
 }
@@ -659,7 +689,7 @@ cudaError_t bh_stats(BhTree *t, BhStats *out, cudaStream_t s)
 {
     unsigned lc[BH_MAX_LEVEL + 2], fl[4];
     double bb[2];
-    unsigned long long cn[2];
+    unsigned long long cn[3];
     BH_TRY(cudaMemcpyAsync(lc, t->level_count, sizeof(lc), cudaMemcpyDeviceToHost, s));
     BH_TRY(cudaMemcpyAsync(fl, t->flags, sizeof(fl), cudaMemcpyDeviceToHost, s));
     BH_TRY(cudaMemcpyAsync(bb, t->bbox, sizeof(double), cudaMemcpyDeviceToHost, s));
@@ -676,6 +706,12 @@ cudaError_t bh_stats(BhTree *t, BhStats *out, cudaStream_t s)
     out->root_border = 2.0 * bb[0];
     out->interactions = cn[0];
     out->visits = cn[1];
+    out->child_tests = cn[2];
+    for (int k = 0; k < BH_STAGES; ++k) {
+        float ms = 0.f;
+        if (t->stages_timed) BH_TRY(cudaEventElapsedTime(&ms, t->ev[k], t->ev[k + 1]));
+        out->stage_ms[k] = ms;
+    }
     return cudaSuccess;
 }
 

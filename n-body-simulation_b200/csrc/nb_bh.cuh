@@ -58,9 +58,14 @@ struct BhTree {
     // radix-sort scratch
     unsigned *hist = nullptr; // [256][sort_blocks]
     unsigned sort_blocks = 0;
-    // visit counters for the bench (optional): [0] interactions, [1] node visits
+    // visit counters for the bench (optional): [0] interactions, [1] node visits,
+    // [2] records tested by a warp (each costs the walk 17 FP64 warp instructions)
     unsigned long long *counters = nullptr;
+    // stage boundaries of the last evaluation issued as plain launches (BhParams::time_stages)
+    cudaEvent_t ev[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    bool stages_timed = false;
 };
+constexpr int BH_STAGES = 6; // keys, sort, order, build, centre of mass, traversal
 
 struct BhParams {
     const double4 *q_cur; // positions + mass, state order (all bodies)
@@ -72,9 +77,11 @@ struct BhParams {
     unsigned flags;       // NB_F_* of nb_common.cuh
     double dt, eps2, G, theta;
     int count_visits;     // 1: accumulate tree.counters
+    int time_stages;      // 1: record the stage events (plain launches only, never while capturing)
 };
 
 size_t bh_bytes(unsigned n);
+unsigned long long bh_node_cap_of(size_t n); // internal-node pool size for n bodies
 cudaError_t bh_alloc(BhTree *t, unsigned n);
 void bh_free(BhTree *t);
 // One force evaluation: bbox -> keys -> sort -> build -> COM -> traversal with the
@@ -91,7 +98,8 @@ cudaError_t bh_morton_order(BhTree *t, const double4 *pos, unsigned n, unsigned 
 struct BhStats {
     unsigned nodes, depth, pool_overflow, stack_overflow;
     double root_border;
-    unsigned long long interactions, visits;
+    unsigned long long interactions, visits, child_tests;
+    float stage_ms[6]; // device time of the stages of the last plainly launched evaluation, else 0
 };
 cudaError_t bh_stats(BhTree *t, BhStats *out, cudaStream_t s);
 

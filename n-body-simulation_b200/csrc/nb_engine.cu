@@ -128,7 +128,11 @@ struct nb_engine {
     void *vel = nullptr, *acc = nullptr;
     double *workspace = nullptr, *partial = nullptr;
     unsigned *counters = nullptr;
-    double *stage_pos = nullptr, *stage_vel = nullptr; // host-packing staging, n*4 / n*3 doubles
+    double *stage_pos = nullptr, *stage_vel = nullptr; // host-packing staging, 4 / 3 doubles per row
+    // host I/O slices (nb_upload_slice / nb_gather_slice): rank r moves rows [r*io_per, (r+1)*io_per)
+    // of the caller's order over PCIe, the rest travels between the GPUs (all-gather of the staging rows)
+    size_t io_per = 0;
+    unsigned *mass_cls = nullptr; // device: [0] all masses equal (FP32 direct), [1] bits of (float)m_0
     double *energy_part = nullptr;
     // frame pipeline (nb_frame_begin / nb_frame_wait), created on first use
     cudaStream_t copy_stream = nullptr;
@@ -185,10 +189,15 @@ int wait_gather(nb_engine *e)
 // In-place all-gather of every rank's slice of `buf`, on the side stream, after
 // everything enqueued on the compute stream so far.  Returns without waiting:
 // consumers call wait_gather().
+int all_gather_bytes(nb_engine *e, void *buf, size_t bytes);
 int all_gather_units(nb_engine *e, void *buf, size_t unit_bytes)
 {
+    return all_gather_bytes(e, buf, (size_t)e->slice_units * unit_bytes);
+}
+// rank r contributes bytes [r*bytes, (r+1)*bytes) of buf
+int all_gather_bytes(nb_engine *e, void *buf, size_t bytes)
+{
     if (e->cfg.world <= 1) return NB_OK;
-    const size_t bytes = (size_t)e->slice_units * unit_bytes;
     const char *send = (const char *)buf + (size_t)e->cfg.rank * bytes;
     NB_CUDA(cudaEventRecord(e->ev_compute, e->stream));
     NB_CUDA(cudaStreamWaitEvent(e->comm_stream, e->ev_compute, 0));
@@ -249,6 +258,7 @@ int launch_force(nb_engine *e, unsigned flags)
         bp.flags = flags;
         bp.dt = p.dt; bp.eps2 = p.eps2; bp.G = p.G; bp.theta = e->cfg.theta;
         bp.count_visits = e->count_visits ? 1 : 0;
+        bp.time_stages = e->bh_graphs_off ? 1 : 0;
         unsigned nl = 0;
         bool done = false;
         if (!e->bh_graphs_off) {
@@ -384,30 +394,52 @@ int deal_curve(nb_engine *e)
     return NB_OK;
 }
 
-int upload(nb_engine *e, const double *pos, const double *vel)
+// rows of the caller's order this rank moves over PCIe in the *_slice calls
+void io_rows(const nb_engine *e, size_t *begin, size_t *count)
+{
+    const size_t b = std::min(e->n, e->io_per * (size_t)e->cfg.rank);
+    *begin = b;
+    *count = std::min(e->n - b, e->io_per);
+}
+
+// sliced: pos / vel hold only this rank's io rows; the other ranks' rows arrive over NVLink
+int upload(nb_engine *e, const double *pos, const double *vel, bool sliced)
 {
     const size_t n = e->n;
     int wrc = wait_gather(e); // an all-gather may still be writing the position buffers
     if (wrc) return wrc;
-    if (n) {
+    if (n && !(sliced && e->cfg.world > 1)) {
         NB_CUDA(cudaMemcpyAsync(e->stage_pos, pos, n * 4 * sizeof(double), cudaMemcpyHostToDevice,
                                 e->stream));
         if (vel)
             NB_CUDA(cudaMemcpyAsync(e->stage_vel, vel, n * 3 * sizeof(double),
                                     cudaMemcpyHostToDevice, e->stream));
+    } else if (n) {
+        size_t b, c;
+        io_rows(e, &b, &c);
+        if (c) {
+            NB_CUDA(cudaMemcpyAsync(e->stage_pos + 4 * b, pos, c * 4 * sizeof(double),
+                                    cudaMemcpyHostToDevice, e->stream));
+            if (vel)
+                NB_CUDA(cudaMemcpyAsync(e->stage_vel + 3 * b, vel, c * 3 * sizeof(double),
+                                        cudaMemcpyHostToDevice, e->stream));
+        }
+        int rc = all_gather_bytes(e, e->stage_pos, e->io_per * 4 * sizeof(double));
+        if (!rc && vel) rc = all_gather_bytes(e, e->stage_vel, e->io_per * 3 * sizeof(double));
+        if (!rc) rc = wait_gather(e);
+        if (rc) return rc;
     }
     // equal masses (the usual N-body initial condition): the FP32 kernel drops m_j from its inner
     // loop and the epilogue multiplies by G*m.  Padding then has to be inert without a zero
-    // mass: it is parked so far away that r^-3 underflows to exactly 0.
-    e->uniform = false;
-    if (e->cfg.precision == NB_PREC_FP32 && !e->bh && n > 0 &&
-        !(e->cfg.tune_flags & (NB_TUNE_SCALAR_FP32 | NB_TUNE_NO_UNIFORM))) {
-        const float m0 = (float)pos[3];
-        bool same = m0 > 0.f;
-        for (size_t i = 1; i < n && same; ++i) same = (float)pos[4 * i + 3] == m0;
-        e->uniform = same;
-        e->uniform_m = (double)m0;
-    }
+    // mass: it is parked so far away that r^-3 underflows to exactly 0.  The masses are
+    // classified on the device (mass_class), from the staged rows; the host reads two words.
+    const bool classify = e->cfg.precision == NB_PREC_FP32 && !e->bh && n > 0 &&
+                          !(e->cfg.tune_flags & (NB_TUNE_SCALAR_FP32 | NB_TUNE_NO_UNIFORM));
+    NB_CUDA(mass_class(e->stage_pos, (unsigned)n, e->mass_cls, classify, e->stream));
+    if (classify) e->st.kernel_launches++;
+    // overflow flags of the tree stay set between evaluations (a truncated tree must be caught
+    // at the next gather) but not across a new state
+    if (e->bh) NB_CUDA(cudaMemsetAsync(e->tree.flags, 0, 2 * sizeof(unsigned), e->stream));
     if (e->user_of) {
         // every rank sees all n bodies, so every rank derives the same order
         unsigned nl = 0;
@@ -429,8 +461,15 @@ int upload(nb_engine *e, const double *pos, const double *vel)
         e->st.kernel_launches += nl + (vel ? 2 : 1);
     }
     NB_CUDA(pack_bodies(e->cfg.precision, e->stage_pos, vel ? e->stage_vel : nullptr, (unsigned)n,
-                        e->n_units, e->q[0], e->q[1], e->vel, e->uniform ? 1.0e18f : 0.f, e->stream));
+                        e->n_units, e->q[0], e->q[1], e->vel, e->mass_cls, e->stream));
     e->st.kernel_launches++;
+    unsigned cls[2] = {0u, 0u};
+    NB_CUDA(cudaMemcpyAsync(cls, e->mass_cls, sizeof(cls), cudaMemcpyDeviceToHost, e->stream));
+    NB_CUDA(cudaStreamSynchronize(e->stream)); // the caller's arrays are free again; cls is in
+    float m0;
+    memcpy(&m0, &cls[1], sizeof(m0));
+    e->uniform = cls[0] != 0u;
+    e->uniform_m = (double)m0;
     e->cur = 0;
     e->state = SYNCED_NOACC;
     e->vel_complete = true;
@@ -506,7 +545,7 @@ void nb_free(nb_engine *e)
     bh_free(&e->tree);
     for (const nb_engine::BhGraph &g : e->bh_graphs) cudaGraphExecDestroy(g.exec);
     void *bufs[] = {e->q[0], e->q[1], e->vel, e->acc, e->workspace, e->partial, e->counters,
-                    e->stage_pos, e->stage_vel, e->energy_part, e->frame_stage[0], e->frame_stage[1],
+                    e->stage_pos, e->stage_vel, e->mass_cls, e->energy_part, e->frame_stage[0], e->frame_stage[1],
                     e->user_of, e->order_tmp, e->morton_tmp, e->chunk_base};
     if (e->copy_stream) cudaStreamSynchronize(e->copy_stream);
     for (void *b : bufs)
@@ -586,6 +625,11 @@ static int init_impl(nb_engine *e, const double *pos, const double *vel)
     e->bh = c.algorithm == NB_ALGO_BARNES_HUT;
     e->count_visits = (c.tune_flags & NB_TUNE_COUNT_VISITS) != 0;
     e->bh_graphs_off = (c.tune_flags & NB_TUNE_NO_GRAPH) != 0;
+    if (e->bh && bh_node_cap_of(e->n) > (unsigned long long)BH_CODE_ID) {
+        // node ids share a 32-bit stack word with the child count and the bucket bit
+        set_err("nb_init", "too many bodies for the Barnes-Hut node ids (27 bits)");
+        return NB_E_INVALID;
+    }
     if (e->bh) NB_CUDA(bh_alloc(&e->tree, (unsigned)e->n));
     if (e->bh && e->n > 1 && !(c.tune_flags & NB_TUNE_NO_REORDER)) {
         NB_CUDA(cudaMalloc(&e->user_of, e->n * sizeof(unsigned)));
@@ -598,8 +642,11 @@ static int init_impl(nb_engine *e, const double *pos, const double *vel)
     NB_CUDA(cudaMalloc(&e->counters, e->plan.counter_bytes ? e->plan.counter_bytes : 16));
     NB_CUDA(cudaMemsetAsync(e->counters, 0, e->plan.counter_bytes ? e->plan.counter_bytes : 16,
                             e->stream));
-    NB_CUDA(cudaMalloc(&e->stage_pos, (e->n ? e->n : 1) * 4 * sizeof(double)));
-    NB_CUDA(cudaMalloc(&e->stage_vel, (e->n ? e->n : 1) * 3 * sizeof(double)));
+    e->io_per = (e->n + (size_t)c.world - 1) / (size_t)c.world;
+    const size_t stage_rows = e->io_per * (size_t)c.world + 1; // whole io slices of every rank
+    NB_CUDA(cudaMalloc(&e->stage_pos, stage_rows * 4 * sizeof(double)));
+    NB_CUDA(cudaMalloc(&e->stage_vel, stage_rows * 3 * sizeof(double)));
+    NB_CUDA(cudaMalloc(&e->mass_cls, 2 * sizeof(unsigned)));
     NB_CUDA(cudaMalloc(&e->energy_part, (size_t)(energy_blocks((unsigned)e->n) + 1) * 2 * sizeof(double)));
 
     if (c.world > 1) {
@@ -615,9 +662,8 @@ static int init_impl(nb_engine *e, const double *pos, const double *vel)
     }
     e->cfg.comm_id = nullptr; // caller's buffer is not kept
 
-    rc = upload(e, pos, vel);
+    rc = upload(e, pos, vel, false);
     if (rc) return rc;
-    NB_CUDA(cudaStreamSynchronize(e->stream));
     e->st.n = e->n;
     e->st.n_padded = (size_t)e->n_units * e->unit_bodies;
     e->st.slice_begin = (size_t)e->i_begin * e->unit_bodies;
@@ -642,6 +688,12 @@ int nb_init(nb_engine **out, const nb_config *cfg, size_t n, const double *pos_x
     }
     if (cfg->algorithm != NB_ALGO_DIRECT && cfg->algorithm != NB_ALGO_BARNES_HUT) {
         set_err("nb_init", "unknown algorithm");
+        return NB_E_INVALID;
+    }
+    if (cfg->algorithm == NB_ALGO_DIRECT && !(cfg->eps2 > 0)) {
+        // the direct kernels include the j = i term like the reference (serial/exhaustive.c:163)
+        // and rely on the softening to make it exactly 0; with eps2 = 0 it is 0 * inf = NaN
+        set_err("nb_init", "the direct sum needs eps2 > 0 (the j = i term is zeroed by the softening)");
         return NB_E_INVALID;
     }
     if (cfg->algorithm == NB_ALGO_BARNES_HUT && cfg->precision != NB_PREC_FP64) {
@@ -676,10 +728,25 @@ int nb_upload(nb_engine *e, const double *pos_xyzm, const double *vel_xyz)
     if (!e || (e->n && !pos_xyzm)) return NB_E_INVALID;
     int rc = set_device(e);
     if (rc) return rc;
-    rc = upload(e, pos_xyzm, vel_xyz);
-    if (rc) return rc;
-    NB_CUDA(cudaStreamSynchronize(e->stream));
+    return upload(e, pos_xyzm, vel_xyz, false);
+}
+
+int nb_io_slice(nb_engine *e, size_t *begin, size_t *count)
+{
+    if (!e || !begin || !count) return NB_E_INVALID;
+    io_rows(e, begin, count);
     return NB_OK;
+}
+
+int nb_upload_slice(nb_engine *e, const double *pos_rows, const double *vel_rows)
+{
+    if (!e) return NB_E_INVALID;
+    size_t b, c;
+    io_rows(e, &b, &c);
+    if (c && !pos_rows) return NB_E_INVALID;
+    int rc = set_device(e);
+    if (rc) return rc;
+    return upload(e, pos_rows, vel_rows, true);
 }
 
 int nb_step(nb_engine *e, int n_steps)
@@ -785,9 +852,9 @@ int nb_host_free(void *p)
     return NB_OK;
 }
 
-int nb_gather(nb_engine *e, double *pos_xyzm, double *vel_xyz)
+// rows [row0, row0 + rows) of the caller's order go to the host arrays (which hold just those rows)
+static int gather_rows(nb_engine *e, double *pos_xyzm, double *vel_xyz, size_t row0, size_t rows)
 {
-    if (!e) return NB_E_INVALID;
     int rc = set_device(e);
     if (rc) return rc;
     const unsigned n = (unsigned)e->n;
@@ -798,8 +865,8 @@ int nb_gather(nb_engine *e, double *pos_xyzm, double *vel_xyz)
         if (rc) return rc;
         NB_CUDA(unpack_bodies(e->cfg.precision, e->vel, n, 3, e->stage_vel, e->user_of, e->stream));
         e->st.kernel_launches++;
-        if (n)
-            NB_CUDA(cudaMemcpyAsync(vel_xyz, e->stage_vel, (size_t)n * 3 * sizeof(double),
+        if (rows)
+            NB_CUDA(cudaMemcpyAsync(vel_xyz, e->stage_vel + 3 * row0, rows * 3 * sizeof(double),
                                     cudaMemcpyDeviceToHost, e->stream));
     }
     if (pos_xyzm) {
@@ -807,8 +874,8 @@ int nb_gather(nb_engine *e, double *pos_xyzm, double *vel_xyz)
         if (rc) return rc;
         NB_CUDA(unpack_bodies(e->cfg.precision, e->q[e->cur], n, 4, e->stage_pos, e->user_of, e->stream));
         e->st.kernel_launches++;
-        if (n)
-            NB_CUDA(cudaMemcpyAsync(pos_xyzm, e->stage_pos, (size_t)n * 4 * sizeof(double),
+        if (rows)
+            NB_CUDA(cudaMemcpyAsync(pos_xyzm, e->stage_pos + 4 * row0, rows * 4 * sizeof(double),
                                     cudaMemcpyDeviceToHost, e->stream));
     }
     NB_CUDA(cudaStreamSynchronize(e->stream));
@@ -818,6 +885,20 @@ int nb_gather(nb_engine *e, double *pos_xyzm, double *vel_xyz)
         if (rc) return rc;
     }
     return NB_OK;
+}
+
+int nb_gather(nb_engine *e, double *pos_xyzm, double *vel_xyz)
+{
+    if (!e) return NB_E_INVALID;
+    return gather_rows(e, pos_xyzm, vel_xyz, 0, e->n);
+}
+
+int nb_gather_slice(nb_engine *e, double *pos_rows, double *vel_rows)
+{
+    if (!e) return NB_E_INVALID;
+    size_t b, c;
+    io_rows(e, &b, &c);
+    return gather_rows(e, pos_rows, vel_rows, b, c);
 }
 
 int nb_accelerations(nb_engine *e, double *acc_xyz)
@@ -896,6 +977,8 @@ int nb_tree_stats(nb_engine *e, nb_tree_info *out)
     out->root_border = bs.root_border;
     out->interactions = bs.interactions;
     out->node_visits = bs.visits;
+    out->child_tests = bs.child_tests;
+    for (int k = 0; k < 6; ++k) out->stage_ms[k] = bs.stage_ms[k];
     out->pool_overflow = (int)bs.pool_overflow;
     out->stack_overflow = (int)bs.stack_overflow;
     if (bs.pool_overflow || bs.stack_overflow) {

@@ -27,6 +27,7 @@ SLICE_ALIGN = {PREC_FP32: 64, PREC_FP64: 128}  # units; nb_direct.cuh kSliceAlig
 
 # every symbol include/nbody_engine.h declares
 ABI_SYMBOLS = ["nb_config_default", "nb_init", "nb_upload", "nb_step", "nb_gather",
+               "nb_io_slice", "nb_upload_slice", "nb_gather_slice",
                "nb_frame_begin", "nb_frame_wait", "nb_host_alloc", "nb_host_free",
                "nb_accelerations", "nb_energy", "nb_sync", "nb_get_stats", "nb_tree_stats", "nb_free",
                "nb_comm_id", "nb_strerror", "nb_last_error", "nb_device_count", "nb_version"]
@@ -54,7 +55,8 @@ class NbStats(C.Structure):
 class NbTreeInfo(C.Structure):
     _fields_ = [("nodes", C.c_uint), ("depth", C.c_uint), ("root_border", C.c_double),
                 ("interactions", C.c_ulonglong), ("node_visits", C.c_ulonglong),
-                ("pool_overflow", C.c_int), ("stack_overflow", C.c_int)]
+                ("pool_overflow", C.c_int), ("stack_overflow", C.c_int),
+                ("child_tests", C.c_ulonglong), ("stage_ms", C.c_double * 6)]
 
 
 class NbodyError(RuntimeError):
@@ -82,6 +84,9 @@ def load_library():
     lib.nb_init.argtypes = [C.POINTER(C.c_void_p), C.POINTER(NbConfig), C.c_size_t,
                             C.c_void_p, C.c_void_p]
     lib.nb_upload.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.nb_io_slice.argtypes = [C.c_void_p, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]
+    lib.nb_upload_slice.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.nb_gather_slice.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     lib.nb_step.argtypes = [C.c_void_p, C.c_int]
     lib.nb_gather.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     lib.nb_frame_begin.argtypes = [C.c_void_p, C.c_void_p]
@@ -210,6 +215,33 @@ class Engine:
 
     def upload_raw(self, pos_ptr, vel_ptr):
         _check(self.lib, self.lib.nb_upload(self.handle, pos_ptr, vel_ptr), "nb_upload")
+
+    def io_slice(self):
+        """(begin, count): the rows of the caller's order this rank moves in upload_slice / gather_slice"""
+        b, c = C.c_size_t(), C.c_size_t()
+        _check(self.lib, self.lib.nb_io_slice(self.handle, C.byref(b), C.byref(c)), "nb_io_slice")
+        return b.value, c.value
+
+    def upload_slice(self, pos_rows, vel_rows):
+        pos = np.ascontiguousarray(pos_rows, dtype=np.float64)
+        vel = np.ascontiguousarray(vel_rows, dtype=np.float64)
+        _check(self.lib, self.lib.nb_upload_slice(self.handle, pos.ctypes.data, vel.ctypes.data),
+               "nb_upload_slice")
+
+    def upload_slice_raw(self, pos_ptr, vel_ptr):
+        _check(self.lib, self.lib.nb_upload_slice(self.handle, pos_ptr, vel_ptr), "nb_upload_slice")
+
+    def gather_slice(self, with_velocities=True):
+        _b, c = self.io_slice()
+        pos = np.empty((c, 4))
+        vel = np.empty((c, 3)) if with_velocities else None
+        _check(self.lib, self.lib.nb_gather_slice(self.handle, pos.ctypes.data,
+                                                  vel.ctypes.data if with_velocities else None),
+               "nb_gather_slice")
+        return pos, vel
+
+    def gather_slice_raw(self, pos_ptr, vel_ptr):
+        _check(self.lib, self.lib.nb_gather_slice(self.handle, pos_ptr, vel_ptr), "nb_gather_slice")
 
     def step(self, n_steps=1):
         _check(self.lib, self.lib.nb_step(self.handle, int(n_steps)), "nb_step")

@@ -150,6 +150,73 @@ def test_bh_node_pool_exhaustion_is_an_error(nb):
         assert "pool" in str(ei.value)
 
 
+def test_bh_overflow_flags_are_cleared_by_a_new_state(nb):
+    """The overflow flags stay set between evaluations (a truncated tree is caught at the next
+    gather) but a new, harmless state uploaded into the same engine must work again."""
+    rng = np.random.default_rng(23)
+    half = 4000
+    a = rng.uniform(-1, 1, (half, 3))
+    pm = np.concatenate([np.concatenate([a, a + 1e-8]), np.ones((2 * half, 1))], axis=1)
+    vel = np.zeros((2 * half, 3))
+    ok = np.concatenate([rng.standard_normal((2 * half, 3)), np.ones((2 * half, 1))], axis=1)
+    with bh_engine(nb, pm, vel) as e:
+        with pytest.raises(nb.NbodyError):
+            e.accelerations()
+            e.gather()
+        with pytest.raises(nb.NbodyError):    # still refused: sticky between evaluations
+            e.gather()
+        e.upload(ok, vel)
+        acc = e.accelerations()
+        e.gather()
+    with nb.Engine(ok, vel, precision=nb.PREC_FP64) as d:
+        err = rel_err(acc, d.accelerations())
+    assert err.max() <= 1.2e-1 and np.median(err) <= 1e-2
+
+
+def _off_centre_system():
+    """A cluster around (10,10,10) plus one body at (-9,-9,-9): the root cube is centred on the
+    ORIGIN (serial/barnes-hut.c:326-338), the centre of mass is far off-centre, and the lone
+    body is more than one root border away from it."""
+    rng = np.random.default_rng(77)
+    n = 400
+    pos = 10.0 + 0.3 * rng.standard_normal((n, 3))
+    pos[0] = (-9.0, -9.0, -9.0)
+    return np.concatenate([pos, rng.uniform(0.1, 1.0, (n, 1))], axis=1)
+
+
+def _tiny_system():
+    """|coord| < 0.05: border^2 of the root is below eps2 = 0.01."""
+    rng = np.random.default_rng(78)
+    n = 300
+    pos = rng.uniform(-0.04, 0.04, (n, 3))
+    return np.concatenate([pos, rng.uniform(0.1, 1.0, (n, 1))], axis=1)
+
+
+@pytest.mark.parametrize("make", [_off_centre_system, _tiny_system])
+def test_bh_root_is_tested_like_any_cell(nb, oracle_lib, make):
+    """The root goes through the same acceptance test as every cell (border / dist < THETA,
+    serial/barnes-hut.c:405,434): with THETA = 0.5 it can never be accepted (both the body and
+    the centre of mass lie in the cube), with THETA = 0 the walk is the exact direct sum.
+    Catches a root threshold that forgets THETA (round-1 advisor finding)."""
+    pm = make()
+    n = len(pm)
+    vel = np.zeros((n, 3))
+    ref = np.zeros((n, 3))
+    ost = np.zeros(5)
+    oracle_lib.orc_bh_acceleration(n, pm, ref, ost.ctypes.data)
+    with bh_engine(nb, pm, vel, tune_flags=nb.TUNE_COUNT_VISITS) as e:
+        acc = e.accelerations()
+        ti = e.tree_stats()
+    scale = np.abs(ref).max()
+    assert np.abs(acc - ref).max() <= 1e-12 * scale
+    assert ti.interactions == int(round(ost[3] * n)) and ti.node_visits == int(round(ost[4] * n))
+    direct = np.zeros((n, 3))
+    oracle_lib.orc_acceleration(n, pm, direct)
+    with bh_engine(nb, pm, vel, theta=0.0) as e:
+        exact = e.accelerations()
+    assert np.abs(exact - direct).max() <= 1e-12 * np.abs(direct).max()
+
+
 def test_bh_fp32_is_refused(nb):
     g = golden("10_bodies")
     with pytest.raises(nb.NbodyError) as ei:

@@ -331,3 +331,56 @@ def test_frame_pipeline_equals_blocking_gather(nb, prec):
         e.step(1)
         e.frame_wait(out)
         assert np.array_equal(out, want[0])
+
+
+def test_direct_sum_refuses_zero_softening(nb):
+    """The direct kernels include j = i like the reference (serial/exhaustive.c:163) and rely on
+    eps2 > 0 to make that term exactly 0; eps2 = 0 would give 0 * inf = NaN for every body."""
+    g = golden("10_bodies")
+    for prec in (nb.PREC_FP64, nb.PREC_FP32):
+        with pytest.raises(nb.NbodyError) as ei:
+            nb.Engine(g["pos_xyzm"], g["vel"], precision=prec, eps2=0.0)
+        assert ei.value.code == -1
+    # Barnes-Hut skips the body's own leaf by index (:411) and works without softening
+    with nb.Engine(g["pos_xyzm"], g["vel"], precision=nb.PREC_FP64, algorithm=nb.ALGO_BARNES_HUT,
+                   eps2=0.0) as e:
+        assert np.isfinite(e.accelerations()).all()
+
+
+@pytest.mark.parametrize("prec", ["fp64", "fp32"])
+def test_slice_io_on_one_rank_is_the_full_io(nb, prec):
+    """world = 1: nb_upload_slice / nb_gather_slice are nb_upload / nb_gather."""
+    g = golden("1k_bodies")
+    P = nb.PREC_FP64 if prec == "fp64" else nb.PREC_FP32
+    with nb.Engine(g["pos_xyzm"], g["vel"], precision=P, dt=g["dt"]) as e:
+        assert e.io_slice() == (0, 1000)
+        e.step(2)
+        p1, v1 = e.gather()
+        e.upload_slice(g["pos_xyzm"], g["vel"])
+        e.step(2)
+        p2, v2 = e.gather_slice()
+    assert np.array_equal(p1, p2) and np.array_equal(v1, v2)
+
+
+def test_equal_mass_detection_runs_on_the_device(nb):
+    """The mass class (equal masses -> m_j hoisted out of the FP32 loop) is decided by a kernel on
+    the staged rows; stats().uniform_mass reports it, and a re-upload with other masses flips it."""
+    rng = np.random.default_rng(5)
+    n = 777
+    pm = np.concatenate([rng.standard_normal((n, 3)), np.full((n, 1), 0.25)], axis=1)
+    vel = np.zeros((n, 3))
+    with nb.Engine(pm, vel, precision=nb.PREC_FP32) as e:
+        assert e.stats().uniform_mass == 1
+        a_uni = e.accelerations()
+        pm2 = pm.copy()
+        pm2[n - 1, 3] = 0.5
+        e.upload(pm2, vel)
+        assert e.stats().uniform_mass == 0
+        e.upload(pm, vel)
+        assert e.stats().uniform_mass == 1
+        assert np.array_equal(e.accelerations(), a_uni)
+    with nb.Engine(pm, vel, precision=nb.PREC_FP32, tune_flags=nb.TUNE_NO_UNIFORM) as e:
+        assert e.stats().uniform_mass == 0
+        assert rel_err(e.accelerations(), a_uni).max() <= 2e-6
+    with nb.Engine(pm, vel, precision=nb.PREC_FP64) as e:
+        assert e.stats().uniform_mass == 0

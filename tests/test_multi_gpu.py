@@ -197,3 +197,39 @@ def test_barnes_hut_ragged_slices_and_orders(nb, n, flags):
 
     for p, v in run_ranks(nb, 2, fn, pm, vel, tune_flags=tf, **kw):
         assert np.array_equal(p, p1) and np.array_equal(v, v1)
+
+
+@pytest.mark.parametrize("algo", ["direct32", "direct64", "bh"])
+@pytest.mark.parametrize("world,n", [(2, 1000), (2, 5), (4, 10_000), (8, 10_000)])
+def test_slice_io_equals_full_io(nb, algo, world, n):
+    """nb_upload_slice / nb_gather_slice: every rank moves only its rows over PCIe, the rest
+    travels between the GPUs.  The state is the one nb_upload of all rows gives, bit for bit,
+    and the gathered slices concatenate to nb_gather's arrays."""
+    need(nb, world)
+    g = golden("10k_bodies_g1")
+    pm, vel = g["pos_xyzm"][:n].copy(), g["vel"][:n].copy()
+    kw = {"direct32": dict(precision=nb.PREC_FP32), "direct64": dict(precision=nb.PREC_FP64),
+          "bh": dict(precision=nb.PREC_FP64, algorithm=nb.ALGO_BARNES_HUT)}[algo]
+    pm2 = pm.copy()
+    pm2[:, :3] *= 1.5                                  # a second state, uploaded by slices
+    pm2[:, 3] = np.linspace(0.1, 0.3, n)
+
+    def fn(e, r):
+        e.step(2)
+        full = e.gather()
+        b, c = e.io_slice()
+        e.upload_slice(pm2[b:b + c], vel[b:b + c])
+        e.step(2)
+        part = e.gather_slice()
+        e.upload(pm2, vel)
+        e.step(2)
+        return full, (b, c), part, e.gather()
+
+    outs = run_ranks(nb, world, fn, pm, vel, dt=g["dt"], **kw)
+    per = (n + world - 1) // world
+    pos_cat = np.concatenate([o[2][0] for o in outs])
+    vel_cat = np.concatenate([o[2][1] for o in outs])
+    for r, (full, (b, c), part, again) in enumerate(outs):
+        assert b == min(n, r * per) and c == min(n - b, per)
+        assert np.array_equal(pos_cat, again[0]) and np.array_equal(vel_cat, again[1])
+        assert np.array_equal(full[0], outs[0][0][0])
