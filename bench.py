@@ -686,16 +686,21 @@ def bh_record(ctx, what, pm, vel, accuracy=True, cpu_baseline=False, single_gpu_
     hp, hs = hbm_peak()
     nodes = ti.nodes
     own = n / ctx.world
-    names = ["keys", "sort", "order", "build", "com", "traversal"]
+    names = ["keys", "sort", "merge", "order", "build", "com", "traversal"]
     # algorithmic bytes per stage per rank: keys read 32 + write 12 per body; sort
-    # 8 passes x 32; order 68; build 560 per cell; centre of mass 360 per cell; traversal = the
-    # cells' child blocks once (512 per cell) + 132 per own body (body, index, v in/out, x out)
-    stage_bytes = [44.0 * n, 256.0 * n, 68.0 * n, 560.0 * nodes, 360.0 * nodes, 512.0 * nodes + 132.0 * own]
+    # 8 passes x 32 (world > 1: keys and sort of the OWN slice only, then ceil(log2 W) merge passes
+    # of 24 B over all keys); order 68; build 560 per cell; centre of mass 360 per cell; traversal =
+    # the cells' child blocks once (512 per cell) + 132 per own body (body, index, v in/out, x out)
+    sorted_here = own if ctx.world > 1 else n
+    merge_passes = int(np.ceil(np.log2(ctx.world))) if ctx.world > 1 else 0
+    stage_bytes = [44.0 * sorted_here, 256.0 * sorted_here, 24.0 * n * merge_passes, 68.0 * n,
+                   560.0 * nodes, 360.0 * nodes, 512.0 * nodes + 132.0 * own]
+    stage_ms = stage_ms[:7]
     stages = {}
     for nm, ms, by in zip(names, stage_ms, stage_bytes):
         gbs = by / (ms * 1e-3) / 1e9 if ms > 0 else None
         stages[nm] = {"ms": ms, "algorithmic_bytes": by, "gbs": gbs, "hbm_frac": (gbs / hp) if gbs else None}
-    trav_ms = stage_ms[5]
+    trav_ms = stage_ms[6]
     fp64_ach = BH_FP64_OPS_PER_TEST * 32.0 * tests_max * 2.0 / (trav_ms * 1e-3) / 1e12 if trav_ms > 0 else None
     total_stage = sum(stage_ms)
     total_bytes = sum(stage_bytes)

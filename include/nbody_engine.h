@@ -84,8 +84,12 @@ typedef struct nb_config {
 #define NB_TUNE_NO_REORDER 32  /* Barnes-Hut: keep the caller's body order on the device */
 #define NB_TUNE_NO_INTERLEAVE 64 /* Barnes-Hut, world > 1: rank slices = contiguous pieces of the Morton curve */
 #define NB_TUNE_NO_GRAPH 128   /* Barnes-Hut: launch the ~75 kernels of an evaluation one by one, not as a CUDA graph */
+#define NB_TUNE_REPLICATED_SORT (1 << 28) /* Barnes-Hut, world > 1: every rank sorts all keys itself (round 1)
+                                             instead of sorting its slice and merging the all-gathered runs */
 /* bits 8..15: force a kernel size class (value - 1); bits 16..23: Barnes-Hut, world > 1: log2 of the
- * pieces per rank the Morton curve is dealt in, + 1 (0 = the default, 32 pieces) */
+ * pieces per rank the Morton curve is dealt in, + 1 (0 = the default, 32 pieces); bits 24..27:
+ * Barnes-Hut, world == 1: sort the keys as that many slices + merge, the way a multi-rank engine
+ * does (rehearsal of the multi-rank sort on one GPU) */
 
 typedef struct nb_stats {
     double last_step_ms;        /* device time (CUDA events on the engine stream) of the last nb_step */
@@ -184,8 +188,9 @@ typedef struct nb_tree_info {
      * instructions each: the FP64-pipe work of the traversal) */
     unsigned long long child_tests;
     /* NB_TUNE_NO_GRAPH: device time (ms) of the stages of the last evaluation -- cube + keys,
-     * radix sort, bodies in Morton order (+ own list), build, centre of mass, traversal; else 0 */
-    double stage_ms[6];
+     * radix sort (world > 1: of the own slice), merge of the ranks' sorted runs (world > 1),
+     * bodies in Morton order (+ own list), build, centre of mass, traversal; else 0 */
+    double stage_ms[8];
 } nb_tree_info;
 int nb_tree_stats(nb_engine *e, nb_tree_info *out);
 

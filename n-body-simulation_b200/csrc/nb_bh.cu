@@ -58,6 +58,48 @@ __global__ void __launch_bounds__(BH_THREADS)
     val[i] = i;
 }
 
+// multi-rank: keys of the bodies [begin, begin + count) only, written in place; indices past the
+// last real body get the all-ones key (63-bit keys never reach it), so they sort behind everybody
+__global__ void __launch_bounds__(BH_THREADS)
+    morton_slice_kernel(const double4 *__restrict__ q, unsigned n, unsigned begin, unsigned count,
+                        const double *__restrict__ bbox, uint64_t *__restrict__ key,
+                        unsigned *__restrict__ val)
+{
+    const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    const unsigned i = begin + t;
+    uint64_t k = ~0ull;
+    if (i < n) {
+        const double4 b = q[i];
+        double border = 2.0 * bbox[0];
+        double cx = 0.0, cy = 0.0, cz = 0.0;
+        k = 0;
+#pragma unroll 1
+        for (int l = 0; l < BH_MAX_LEVEL; ++l) {
+            const double q4 = border / 4;
+            const int z = b.z >= cz, y = b.y >= cy, x = b.x >= cx;
+            k = (k << 3) | (uint64_t)(z * 4 + y * 2 + x);
+            cx += x ? q4 : -q4;
+            cy += y ? q4 : -q4;
+            cz += z ? q4 : -q4;
+            border /= 2;
+        }
+    }
+    key[i] = k;
+    val[i] = i;
+}
+
+// the cube of all bodies from the ranks' partial maxima (max is exact: any order gives the
+// single-rank value)
+__global__ void bbox_combine_kernel(const double *__restrict__ parts, unsigned world, double *bbox)
+{
+    if (threadIdx.x == 0) {
+        double m = 0.0;
+        for (unsigned r = 0; r < world; ++r) m = fmax(m, parts[r]);
+        bbox[0] = m;
+    }
+}
+
 // positions in Morton order + the list of sorted indices this rank integrates
 __global__ void __launch_bounds__(BH_THREADS)
     gather_sorted_kernel(const double4 *__restrict__ q, const unsigned *__restrict__ perm,
@@ -553,16 +595,20 @@ size_t bh_bytes(unsigned n)
         if (_e != cudaSuccess) return _e;  \
     } while (0)
 
-cudaError_t bh_alloc(BhTree *t, unsigned n)
+cudaError_t bh_alloc(BhTree *t, unsigned n, unsigned n_keys, unsigned parts)
 {
     const size_t nn = n ? n : 1;
     t->n = n;
+    t->n_keys = n_keys > n ? n_keys : n;
     t->node_cap = bh_node_cap(n);
     t->sort_blocks = bh_sort_blocks(n);
+    const size_t nk = t->n_keys ? t->n_keys : 1;
     for (int b = 0; b < 2; ++b) {
-        BH_TRY(cudaMalloc(&t->key[b], nn * sizeof(uint64_t)));
-        BH_TRY(cudaMalloc(&t->val[b], nn * sizeof(unsigned)));
+        BH_TRY(cudaMalloc(&t->key[b], nk * sizeof(uint64_t)));
+        BH_TRY(cudaMalloc(&t->val[b], nk * sizeof(unsigned)));
     }
+    BH_TRY(cudaMalloc(&t->bbox_parts, (parts ? parts : 1) * sizeof(double)));
+    BH_TRY(cudaMemset(t->bbox_parts, 0, (parts ? parts : 1) * sizeof(double)));
     BH_TRY(cudaMalloc(&t->spos, nn * sizeof(double4)));
     BH_TRY(cudaMalloc(&t->own, nn * sizeof(unsigned)));
     BH_TRY(cudaMalloc(&t->own_counts, (nn / OWN_TILE + 2) * sizeof(unsigned)));
@@ -580,7 +626,10 @@ cudaError_t bh_alloc(BhTree *t, unsigned n)
     BH_TRY(cudaMalloc(&t->hist, ((size_t)256 * t->sort_blocks + 256) * sizeof(unsigned)));
     BH_TRY(cudaMalloc(&t->counters, 4 * sizeof(unsigned long long)));
     BH_TRY(cudaMemset(t->counters, 0, 4 * sizeof(unsigned long long)));
-    for (int k = 0; k < BH_STAGES + 1; ++k) BH_TRY(cudaEventCreate(&t->ev[k]));
+    for (int k = 0; k < BH_STAGES; ++k) {
+        BH_TRY(cudaEventCreate(&t->evb[k]));
+        BH_TRY(cudaEventCreate(&t->eve[k]));
+    }
     return cudaSuccess;
 }
 
@@ -588,11 +637,13 @@ void bh_free(BhTree *t)
 {
     void *bufs[] = {t->key[0], t->key[1], t->val[0], t->val[1], t->spos, t->own, t->own_counts, t->com, t->child,
                     t->first, t->count, t->level, t->cblock, t->pslot, t->level_count, t->flags, t->bbox, t->hist,
-                    t->counters};
+                    t->counters, t->bbox_parts};
     for (void *b : bufs)
         if (b) cudaFree(b);
-    for (cudaEvent_t ev : t->ev)
-        if (ev) cudaEventDestroy(ev);
+    for (int k = 0; k < BH_STAGES; ++k) {
+        if (t->evb[k]) cudaEventDestroy(t->evb[k]);
+        if (t->eve[k]) cudaEventDestroy(t->eve[k]);
+    }
     *t = BhTree();
 }
 
@@ -614,60 +665,62 @@ cudaError_t bh_morton_order(BhTree *t, const double4 *pos, unsigned n, unsigned 
     return cudaGetLastError();
 }
 
-cudaError_t bh_evaluate(BhTree *t, const BhParams &p, cudaStream_t s, unsigned *launches)
+// stage boundaries for nb_tree_stats (plain launches only: never inside a graph capture)
+enum { ST_KEYS = 0, ST_SORT, ST_MERGE, ST_ORDER, ST_BUILD, ST_COM, ST_TRAV };
+static cudaError_t stage_begin(BhTree *t, const BhParams &p, int k, cudaStream_t s)
+{
+    if (p.time_stages) t->stage_seen[k] = true;
+    return p.time_stages ? cudaEventRecord(t->evb[k], s) : cudaSuccess;
+}
+static cudaError_t stage_end(BhTree *t, const BhParams &p, int k, cudaStream_t s)
+{
+    return p.time_stages ? cudaEventRecord(t->eve[k], s) : cudaSuccess;
+}
+
+// everything after the sorted (key, index) sequence exists in key[t->sorted] / val[t->sorted]:
+// bodies in Morton order, own list, build, centre of mass, traversal with the fused epilogue
+static cudaError_t bh_after_sort(BhTree *t, const BhParams &p, cudaStream_t s, unsigned *launches)
 {
     const unsigned n = p.n;
     unsigned nl = 0;
-    if (n == 0) return cudaSuccess;
     const unsigned nblk = (n + BH_THREADS - 1) / BH_THREADS;
     const unsigned wide = nblk < 148u * 8u ? nblk : 148u * 8u; // grid-stride kernels: 8 CTAs per SM
-    // stage boundaries for nb_tree_stats (plain launches only: not inside a graph capture)
-    int stage = 0;
-    auto mark = [&]() -> cudaError_t {
-        return p.time_stages ? cudaEventRecord(t->ev[stage++], s) : cudaSuccess;
-    };
-    t->stages_timed = false;
-    BH_TRY(mark()); // 0: cube + keys
-    reset_kernel<<<1, 32, 0, s>>>(t->level_count, t->flags, t->bbox, t->first, t->count, t->level,
-                                  n, t->counters, p.count_visits);
-    bbox_kernel<<<wide, BH_THREADS, 0, s>>>(p.q_cur, n, reinterpret_cast<unsigned long long *>(t->bbox));
-    morton_kernel<<<nblk, BH_THREADS, 0, s>>>(p.q_cur, n, t->bbox, t->key[0], t->val[0]);
-    nl += 3;
-    BH_TRY(mark()); // 1: sort
-    BH_TRY(bh_radix_sort(t, n, 3 * BH_MAX_LEVEL, s, &nl));
-    BH_TRY(mark()); // 2: bodies in Morton order + own list
-    gather_sorted_kernel<<<nblk, BH_THREADS, 0, s>>>(p.q_cur, t->val[0], n, t->spos);
+    const uint64_t *skey = t->key[t->sorted];
+    const unsigned *perm = t->val[t->sorted];
+    BH_TRY(stage_begin(t, p, ST_ORDER, s));
+    gather_sorted_kernel<<<nblk, BH_THREADS, 0, s>>>(p.q_cur, perm, n, t->spos);
     ++nl;
     const bool sliced = !(p.own_begin == 0 && p.own_end >= n);
     if (sliced) {
         const unsigned tiles = (n + OWN_TILE - 1) / OWN_TILE;
-        own_count_kernel<<<tiles, OWN_TILE, 0, s>>>(t->val[0], n, p.own_begin, p.own_end, t->own_counts);
+        own_count_kernel<<<tiles, OWN_TILE, 0, s>>>(perm, n, p.own_begin, p.own_end, t->own_counts);
         BH_TRY(bh_exclusive_scan(t->own_counts, tiles, &t->flags[2], s));
-        own_write_kernel<<<tiles, OWN_TILE, 0, s>>>(t->val[0], n, p.own_begin, p.own_end,
+        own_write_kernel<<<tiles, OWN_TILE, 0, s>>>(perm, n, p.own_begin, p.own_end,
                                                     t->own_counts, t->own);
         nl += 3;
     }
-    BH_TRY(mark()); // 3: build
+    BH_TRY(stage_end(t, p, ST_ORDER, s));
     if (n >= 2) {
-        BuildArgs ba{t->key[0], t->first, t->count, t->level, t->child, t->level_count, t->flags,
+        BH_TRY(stage_begin(t, p, ST_BUILD, s));
+        BuildArgs ba{skey, t->first, t->count, t->level, t->child, t->level_count, t->flags,
                      t->node_cap, t->spos, t->cblock, t->pslot};
         // a level holds at most n/2 nodes, 8 lanes each
         const unsigned bgrid = min(wide, (n / 2 * 8 + BH_THREADS - 1) / BH_THREADS + 1);
         for (int L = 0; L < BH_MAX_LEVEL; ++L) build_level_kernel<<<bgrid, BH_THREADS, 0, s>>>(ba, L);
-        BH_TRY(mark()); // 4: centre of mass
+        BH_TRY(stage_end(t, p, ST_BUILD, s));
+        BH_TRY(stage_begin(t, p, ST_COM, s));
         const unsigned cgrid = min(wide, (n / 2 + BH_THREADS - 1) / BH_THREADS + 1);
         for (int L = BH_MAX_LEVEL; L >= 0; --L)
             com_level_kernel<<<cgrid, BH_THREADS, 0, s>>>(t->spos, t->child, t->first, t->count,
                                                           t->level_count, t->com, L, t->node_cap, t->bbox,
                                                           t->cblock, t->pslot, p.theta, p.eps2);
+        BH_TRY(stage_end(t, p, ST_COM, s));
         nl += 2 * BH_MAX_LEVEL + 1;
-    } else {
-        BH_TRY(mark());
     }
-    BH_TRY(mark()); // 5: traversal
+    BH_TRY(stage_begin(t, p, ST_TRAV, s));
     TravArgs ta;
     ta.spos = t->spos; ta.com = t->com; ta.cblock = t->cblock;
-    ta.first = t->first; ta.count = t->count; ta.perm = t->val[0];
+    ta.first = t->first; ta.count = t->count; ta.perm = perm;
     ta.own = sliced ? t->own : nullptr;
     ta.bbox = t->bbox; ta.flags = t->flags; ta.counters = t->counters;
     ta.n_own_static = n;
@@ -679,10 +732,100 @@ cudaError_t bh_evaluate(BhTree *t, const BhParams &p, cudaStream_t s, unsigned *
         else traverse_kernel<false><<<tgrid, TRAV_WARPS * 32, 0, s>>>(ta);
         ++nl;
     }
-    BH_TRY(mark()); // 6: end
+    BH_TRY(stage_end(t, p, ST_TRAV, s));
     t->stages_timed = p.time_stages != 0;
     if (launches) *launches += nl;
     return cudaGetLastError();
+}
+
+cudaError_t bh_evaluate(BhTree *t, const BhParams &p, cudaStream_t s, unsigned *launches)
+{
+    const unsigned n = p.n;
+    unsigned nl = 0;
+    if (n == 0) return cudaSuccess;
+    const unsigned nblk = (n + BH_THREADS - 1) / BH_THREADS;
+    const unsigned wide = nblk < 148u * 8u ? nblk : 148u * 8u;
+    for (bool &b : t->stage_seen) b = false;
+    t->stages_timed = false;
+    BH_TRY(stage_begin(t, p, ST_KEYS, s));
+    reset_kernel<<<1, 32, 0, s>>>(t->level_count, t->flags, t->bbox, t->first, t->count, t->level,
+                                  n, t->counters, p.count_visits);
+    bbox_kernel<<<wide, BH_THREADS, 0, s>>>(p.q_cur, n, reinterpret_cast<unsigned long long *>(t->bbox));
+    morton_kernel<<<nblk, BH_THREADS, 0, s>>>(p.q_cur, n, t->bbox, t->key[0], t->val[0]);
+    nl += 3;
+    BH_TRY(stage_end(t, p, ST_KEYS, s));
+    if (p.emulate_runs > 1) {
+        // single-rank rehearsal of the multi-rank sort (tests on a one-GPU box): the key sequence
+        // is cut into `emulate_runs` slices, each sorted on its own, the runs merged
+        const unsigned runs = (unsigned)p.emulate_runs;
+        unsigned per = (n + runs - 1) / runs;
+        per = (per + 127u) / 128u * 128u;
+        if ((unsigned long long)per * runs > t->n_keys) return cudaErrorInvalidValue;
+        BH_TRY(stage_begin(t, p, ST_SORT, s));
+        for (unsigned r = 0; r < runs; ++r) {
+            morton_slice_kernel<<<(per + BH_THREADS - 1) / BH_THREADS, BH_THREADS, 0, s>>>(
+                p.q_cur, n, r * per, per, t->bbox, t->key[0], t->val[0]);
+            ++nl;
+            BH_TRY(bh_radix_sort(t, per, 3 * BH_MAX_LEVEL + 1, s, &nl, r * per));
+        }
+        BH_TRY(stage_end(t, p, ST_SORT, s));
+        BH_TRY(stage_begin(t, p, ST_MERGE, s));
+        BH_TRY(bh_merge_runs(t, runs * per, per, s, &nl));
+        BH_TRY(stage_end(t, p, ST_MERGE, s));
+    } else {
+        BH_TRY(stage_begin(t, p, ST_SORT, s));
+        BH_TRY(bh_radix_sort(t, n, 3 * BH_MAX_LEVEL, s, &nl));
+        BH_TRY(stage_end(t, p, ST_SORT, s));
+        t->sorted = 0;
+    }
+    if (launches) *launches += nl;
+    return bh_after_sort(t, p, s, launches);
+}
+
+cudaError_t bh_slice_max(BhTree *t, const double4 *q, unsigned n, unsigned rank, unsigned per,
+                         cudaStream_t s, unsigned *launches)
+{
+    const unsigned long long b = (unsigned long long)rank * per;
+    const unsigned begin = (unsigned)(b < n ? b : n), count = min(per, n - begin);
+    BH_TRY(cudaMemsetAsync(t->bbox_parts + rank, 0, sizeof(double), s));
+    if (count) {
+        const unsigned nblk = (count + BH_THREADS - 1) / BH_THREADS;
+        bbox_kernel<<<nblk < 148u * 8u ? nblk : 148u * 8u, BH_THREADS, 0, s>>>(
+            q + begin, count, reinterpret_cast<unsigned long long *>(t->bbox_parts + rank));
+        if (launches) ++*launches;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t bh_slice_sort(BhTree *t, const BhParams &p, unsigned rank, unsigned world, unsigned per,
+                          cudaStream_t s, unsigned *launches)
+{
+    unsigned nl = 0;
+    for (bool &b : t->stage_seen) b = false;
+    t->stages_timed = false;
+    BH_TRY(stage_begin(t, p, ST_KEYS, s));
+    reset_kernel<<<1, 32, 0, s>>>(t->level_count, t->flags, t->bbox, t->first, t->count, t->level,
+                                  p.n, t->counters, p.count_visits);
+    bbox_combine_kernel<<<1, 32, 0, s>>>(t->bbox_parts, world, t->bbox);
+    const unsigned begin = rank * per;
+    morton_slice_kernel<<<(per + BH_THREADS - 1) / BH_THREADS, BH_THREADS, 0, s>>>(
+        p.q_cur, p.n, begin, per, t->bbox, t->key[0], t->val[0]);
+    nl += 3;
+    BH_TRY(stage_end(t, p, ST_KEYS, s));
+    BH_TRY(stage_begin(t, p, ST_SORT, s));
+    BH_TRY(bh_radix_sort(t, per, 3 * BH_MAX_LEVEL + 1, s, &nl, begin)); // + 1: the padding key's top bit
+    BH_TRY(stage_end(t, p, ST_SORT, s));
+    if (launches) *launches += nl;
+    return cudaGetLastError();
+}
+
+cudaError_t bh_finish(BhTree *t, const BhParams &p, unsigned world, unsigned per, cudaStream_t s,
+                      unsigned *launches)
+{
+    BH_TRY(stage_begin(t, p, ST_MERGE, s));
+    BH_TRY(bh_merge_runs(t, world * per, per, s, launches));
+    BH_TRY(stage_end(t, p, ST_MERGE, s));
+    return bh_after_sort(t, p, s, launches);
 }
 
 cudaError_t bh_stats(BhTree *t, BhStats *out, cudaStream_t s)
@@ -709,7 +852,7 @@ cudaError_t bh_stats(BhTree *t, BhStats *out, cudaStream_t s)
     out->child_tests = cn[2];
     for (int k = 0; k < BH_STAGES; ++k) {
         float ms = 0.f;
-        if (t->stages_timed) BH_TRY(cudaEventElapsedTime(&ms, t->ev[k], t->ev[k + 1]));
+        if (t->stages_timed && t->stage_seen[k]) BH_TRY(cudaEventElapsedTime(&ms, t->evb[k], t->eve[k]));
         out->stage_ms[k] = ms;
     }
     return cudaSuccess;

@@ -34,6 +34,9 @@ constexpr unsigned BH_CODE_BUCKET = 1u << 30; // a finest-level cell: bodies sum
 // arrays.
 struct BhTree {
     unsigned n = 0;        // real bodies
+    unsigned n_keys = 0;   // key / val capacity: n, or (multi-rank) the padded slices of all ranks
+    int sorted = 0;        // which of key[.] / val[.] holds the sorted sequence of the evaluation
+    double *bbox_parts = nullptr; // multi-rank: max |coord| of every rank's slice (all-gathered)
     unsigned node_cap = 0; // internal-node pool size
     // per body
     uint64_t *key[2] = {nullptr, nullptr}; // Morton keys, ping-pong for the sort
@@ -62,10 +65,11 @@ struct BhTree {
     // [2] records tested by a warp (each costs the walk 17 FP64 warp instructions)
     unsigned long long *counters = nullptr;
     // stage boundaries of the last evaluation issued as plain launches (BhParams::time_stages)
-    cudaEvent_t ev[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t evb[7] = {}, eve[7] = {};
+    bool stage_seen[7] = {};
     bool stages_timed = false;
 };
-constexpr int BH_STAGES = 6; // keys, sort, order, build, centre of mass, traversal
+constexpr int BH_STAGES = 7; // keys, sort, merge (multi-rank), order, build, centre of mass, traversal
 
 struct BhParams {
     const double4 *q_cur; // positions + mass, state order (all bodies)
@@ -78,16 +82,33 @@ struct BhParams {
     double dt, eps2, G, theta;
     int count_visits;     // 1: accumulate tree.counters
     int time_stages;      // 1: record the stage events (plain launches only, never while capturing)
+    int emulate_runs;     // > 1 (single rank): sort as that many slices + merge, like a multi-rank engine
 };
 
 size_t bh_bytes(unsigned n);
 unsigned long long bh_node_cap_of(size_t n); // internal-node pool size for n bodies
-cudaError_t bh_alloc(BhTree *t, unsigned n);
+// n_keys >= n: capacity of the key / index arrays (padded slices of all ranks); parts: ranks
+cudaError_t bh_alloc(BhTree *t, unsigned n, unsigned n_keys = 0, unsigned parts = 1);
 void bh_free(BhTree *t);
 // One force evaluation: bbox -> keys -> sort -> build -> COM -> traversal with the
 // kick/drift epilogue selected by p.flags.  Returns the number of kernel launches
 // through *launches.
 cudaError_t bh_evaluate(BhTree *t, const BhParams &p, cudaStream_t s, unsigned *launches);
+// The same evaluation for a multi-rank engine, cut where the ranks exchange data:
+//   bh_slice_max   : max |coord| of the own slice of `q` -> bbox_parts[rank]      (then all-gather
+//                    of bbox_parts; it runs before the positions are exchanged)
+//   bh_slice_sort  : cube from all ranks' maxima, keys of the own slice, sorted in place at
+//                    [rank * per, (rank + 1) * per) of key[0] / val[0] (padding keys = all ones)
+//                    -- needs only the own positions, so it overlaps the all-gather of the others'
+//                    (then all-gather of the sorted runs)
+//   bh_finish      : merge of the W runs, then order / build / centre of mass / traversal as in
+//                    bh_evaluate.  The merged sequence equals the full sort, so does the tree.
+cudaError_t bh_slice_max(BhTree *t, const double4 *q, unsigned n, unsigned rank, unsigned per,
+                         cudaStream_t s, unsigned *launches);
+cudaError_t bh_slice_sort(BhTree *t, const BhParams &p, unsigned rank, unsigned world, unsigned per,
+                          cudaStream_t s, unsigned *launches);
+cudaError_t bh_finish(BhTree *t, const BhParams &p, unsigned world, unsigned per, cudaStream_t s,
+                      unsigned *launches);
 // Morton order of n bodies given as x,y,z,m rows: order[k] = row of the body of rank k
 // (the keys and the sort of bh_evaluate, without the tree).  Used once per upload to lay
 // the state out along the curve, so that rank slices are compact regions of space.
@@ -99,13 +120,18 @@ struct BhStats {
     unsigned nodes, depth, pool_overflow, stack_overflow;
     double root_border;
     unsigned long long interactions, visits, child_tests;
-    float stage_ms[6]; // device time of the stages of the last plainly launched evaluation, else 0
+    float stage_ms[7]; // device time of the stages of the last plainly launched evaluation, else 0
 };
 cudaError_t bh_stats(BhTree *t, BhStats *out, cudaStream_t s);
 
 // stable LSD radix sort of (key, val) pairs on 8-bit digits (nb_bh_sort.cu);
 // result in key[0], val[0].  bits: number of low key bits that matter.
-cudaError_t bh_radix_sort(BhTree *t, unsigned n, int bits, cudaStream_t s, unsigned *launches);
+// offset: sort the n pairs starting at key[.] + offset / val[.] + offset in place (own-slice sort)
+cudaError_t bh_radix_sort(BhTree *t, unsigned n, int bits, cudaStream_t s, unsigned *launches,
+                          unsigned offset = 0);
+// key[0] / val[0] hold total / run sorted runs of length `run` (the last may be short): merges
+// them; the result is in key[t->sorted] / val[t->sorted]
+cudaError_t bh_merge_runs(BhTree *t, unsigned total, unsigned run, cudaStream_t s, unsigned *launches);
 unsigned bh_sort_blocks(unsigned n);
 // in-place exclusive prefix sum of `len` counters (one CTA); the grand total goes to *total
 cudaError_t bh_exclusive_scan(unsigned *a, unsigned len, unsigned *total, cudaStream_t s);

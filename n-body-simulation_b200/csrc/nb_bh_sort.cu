@@ -164,7 +164,8 @@ cudaError_t bh_exclusive_scan(unsigned *a, unsigned len, unsigned *total, cudaSt
 
 unsigned bh_sort_blocks(unsigned n) { return n ? (n + SORT_TILE - 1) / SORT_TILE : 1u; }
 
-cudaError_t bh_radix_sort(BhTree *t, unsigned n, int bits, cudaStream_t s, unsigned *launches)
+cudaError_t bh_radix_sort(BhTree *t, unsigned n, int bits, cudaStream_t s, unsigned *launches,
+                          unsigned offset)
 {
     if (n == 0) return cudaSuccess;
     const unsigned nb = bh_sort_blocks(n);
@@ -172,12 +173,93 @@ cudaError_t bh_radix_sort(BhTree *t, unsigned n, int bits, cudaStream_t s, unsig
     if (passes & 1) ++passes; // an even number of passes leaves the result in buffer 0
     for (int p = 0; p < passes; ++p) {
         const int in = p & 1, out = in ^ 1, shift = 8 * p;
-        digit_histogram<<<nb, SORT_THREADS, 0, s>>>(t->key[in], n, shift, nb, t->hist);
+        digit_histogram<<<nb, SORT_THREADS, 0, s>>>(t->key[in] + offset, n, shift, nb, t->hist);
         scan_rows<<<256, 1024, 0, s>>>(t->hist, nb, t->hist + (size_t)256 * nb);
-        scatter<<<nb, SORT_THREADS, 0, s>>>(t->key[in], t->val[in], t->key[out], t->val[out], n,
-                                            shift, nb, t->hist, t->hist + (size_t)256 * nb);
+        scatter<<<nb, SORT_THREADS, 0, s>>>(t->key[in] + offset, t->val[in] + offset, t->key[out] + offset,
+                                            t->val[out] + offset, n, shift, nb, t->hist,
+                                            t->hist + (size_t)256 * nb);
         if (launches) *launches += 3;
     }
+    return cudaGetLastError();
+}
+
+// ---- bottom-up merge of sorted runs (multi-rank engines) --------------------------------------
+// Every rank sorts the keys of its own slice; the sorted (key, index) runs are all-gathered and
+// merged here: one pass merges adjacent runs of length `seg` pairwise (merge path: the CTA of an
+// output tile finds its two input ranges by binary search on the tile's diagonals, stages them in
+// shared memory, and every thread merges 8 outputs from its own diagonal).  Ties take the left
+// run first, so equal keys stay in index order like in the stable radix sort: the merged
+// sequence IS what bh_radix_sort gives on all keys.  ceil(log2(W)) passes of 24 B/key instead of
+// 8 radix passes of 32 B/key over all bodies on every rank.
+namespace {
+constexpr int MERGE_THREADS = 256;
+constexpr int MERGE_ITEMS = 8;
+constexpr int MERGE_TILE = MERGE_THREADS * MERGE_ITEMS;
+
+// how many elements of A are among the first d outputs of merge(A, B); ties: A first
+__device__ __forceinline__ unsigned merge_path(const uint64_t *A, unsigned la, const uint64_t *B,
+                                               unsigned lb, unsigned d)
+{
+    unsigned lo = d > lb ? d - lb : 0u, hi = d < la ? d : la;
+    while (lo < hi) {
+        const unsigned mid = (lo + hi) >> 1;
+        if (A[mid] <= B[d - 1 - mid]) lo = mid + 1;
+        else hi = mid;
+    }
+    return lo;
+}
+
+__global__ void __launch_bounds__(MERGE_THREADS)
+    merge_pass_kernel(const uint64_t *__restrict__ kin, const unsigned *__restrict__ vin,
+                      uint64_t *__restrict__ kout, unsigned *__restrict__ vout, unsigned total,
+                      unsigned seg, unsigned tiles_per_pair)
+{
+    __shared__ uint64_t sk[MERGE_TILE];
+    __shared__ unsigned sv[MERGE_TILE];
+    __shared__ unsigned s_a[2];
+    const unsigned pair = blockIdx.x / tiles_per_pair, tile = blockIdx.x % tiles_per_pair;
+    const unsigned long long p0l = (unsigned long long)pair * 2ull * seg;
+    if (p0l >= total) return;
+    const unsigned p0 = (unsigned)p0l;
+    const unsigned la = min(seg, total - p0), lb = min(seg, total - p0 - la);
+    const unsigned len = la + lb, d0 = tile * MERGE_TILE;
+    if (d0 >= len) return;
+    const unsigned d1 = min(d0 + (unsigned)MERGE_TILE, len);
+    const uint64_t *A = kin + p0, *B = kin + p0 + la;
+    if (threadIdx.x == 0) s_a[0] = merge_path(A, la, B, lb, d0);
+    if (threadIdx.x == 32) s_a[1] = merge_path(A, la, B, lb, d1);
+    __syncthreads();
+    const unsigned a0 = s_a[0], a1 = s_a[1], b0 = d0 - a0;
+    const unsigned na = a1 - a0, nb = (d1 - a1) - b0, cnt = na + nb;
+    for (unsigned i = threadIdx.x; i < cnt; i += MERGE_THREADS) {
+        const unsigned src = i < na ? p0 + a0 + i : p0 + la + b0 + (i - na);
+        sk[i] = kin[src];
+        sv[i] = vin[src];
+    }
+    __syncthreads();
+    const unsigned t0 = min(threadIdx.x * (unsigned)MERGE_ITEMS, cnt), t1 = min(t0 + (unsigned)MERGE_ITEMS, cnt);
+    unsigned sa = merge_path(sk, na, sk + na, nb, t0), sb = t0 - sa;
+    for (unsigned o = t0; o < t1; ++o) {
+        const bool take_a = sb >= nb || (sa < na && sk[sa] <= sk[na + sb]);
+        const unsigned idx = take_a ? sa++ : na + sb++;
+        kout[p0 + d0 + o] = sk[idx];
+        vout[p0 + d0 + o] = sv[idx];
+    }
+}
+} // namespace
+
+cudaError_t bh_merge_runs(BhTree *t, unsigned total, unsigned run, cudaStream_t s, unsigned *launches)
+{
+    int in = 0;
+    for (unsigned long long seg = run; seg < total; seg *= 2) {
+        const unsigned tpp = (unsigned)((2ull * seg + MERGE_TILE - 1) / MERGE_TILE);
+        const unsigned pairs = (unsigned)((total + 2ull * seg - 1) / (2ull * seg));
+        merge_pass_kernel<<<pairs * tpp, MERGE_THREADS, 0, s>>>(t->key[in], t->val[in], t->key[in ^ 1],
+                                                                 t->val[in ^ 1], total, (unsigned)seg, tpp);
+        in ^= 1;
+        if (launches) ++*launches;
+    }
+    t->sorted = in;
     return cudaGetLastError();
 }
 

@@ -341,6 +341,287 @@ __global__ void __launch_bounds__(NW * 32, MINB)
     }
 }
 
+
+// ======================= i-packed kernel (round 2, the large size class) =======================
+// The packed lanes hold two I-bodies instead of two j-bodies; the j-body is a broadcast scalar
+// operand (SASS: "FADD2 R, -Ri.F32x2.HI_LO, Rj.F32", eps2 as an immediate of the first FFMA2).
+// Accumulators are then per i-body only -- half as many registers as the j-packed form -- so a
+// thread carries QPT = 2 quads = 8 i-bodies in 128 registers: half the LDS and loop overhead per
+// interaction, four independent dependency chains per j.  Measured with tools/innerloop_bench.cu
+// (profiles/r2_innerloop_variants_1.jsonl): 12.6-12.9 clk per interaction-warp against 13.2 for
+// the j-packed loop; the same file shows the north star's warp-shuffle broadcast of j-bodies at
+// 13.4-15.8 clk (SHFL fan-out costs issue slots the loop does not have).
+template <bool UNI, int NP>
+__device__ __forceinline__ void one_j_ipacked(float xj, float yj, float zj, float mj,
+                                              const float2 (&xi)[NP], const float2 (&yi)[NP],
+                                              const float2 (&zi)[NP], float e2s, float2 (&ax)[NP],
+                                              float2 (&ay)[NP], float2 (&az)[NP])
+{
+#pragma unroll
+    for (int p = 0; p < NP; ++p) {
+        const float2 dx = __fadd2_rn(make_float2(xj, xj), make_float2(-xi[p].x, -xi[p].y));
+        const float2 dy = __fadd2_rn(make_float2(yj, yj), make_float2(-yi[p].x, -yi[p].y));
+        const float2 dz = __fadd2_rn(make_float2(zj, zj), make_float2(-zi[p].x, -zi[p].y));
+        float2 r2 = __ffma2_rn(dx, dx, make_float2(e2s, e2s));
+        r2 = __ffma2_rn(dy, dy, r2);
+        r2 = __ffma2_rn(dz, dz, r2);
+        const float2 ri = make_float2(rsqrt_approx(r2.x), rsqrt_approx(r2.y));
+        const float2 ri2 = __fmul2_rn(ri, ri);
+        const float2 s = UNI ? __fmul2_rn(ri2, ri) : __fmul2_rn(ri2, __fmul2_rn(make_float2(mj, mj), ri));
+        ax[p] = __ffma2_rn(dx, s, ax[p]);
+        ay[p] = __ffma2_rn(dy, s, ay[p]);
+        az[p] = __ffma2_rn(dz, s, az[p]);
+    }
+}
+
+// MODE: 1 general masses, 2 uniform mass.  QPT quads (4 i-bodies each) per thread.
+template <int NW, int TQ, int MODE, int MINB, int QPT>
+__global__ void __launch_bounds__(NW * 32, MINB)
+    direct_f32_ip_kernel(const StepParams p)
+{
+    constexpr int NT = NW * 32;      // threads
+    constexpr int NP = 2 * QPT;      // i-pairs per thread
+    constexpr int QPB = NT * QPT;    // quads per i-block
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float4(*tiles)[TQ * 4] = reinterpret_cast<float4(*)[TQ * 4]>(smem_raw);
+    // FP64 running sums, 6 per i-pair, touched once per tile
+    double(*dacc)[NT] = reinterpret_cast<double(*)[NT]>(smem_raw + (size_t)STAGES * TQ * 4 * sizeof(float4));
+    __shared__ __align__(8) uint64_t full_bar[STAGES];
+    __shared__ __align__(8) uint64_t empty_bar[STAGES];
+    __shared__ unsigned s_last;
+
+    const int lane = threadIdx.x & 31;
+    const float4 *__restrict__ q = static_cast<const float4 *>(p.q_cur);
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], NW);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    const unsigned long long w0 = p.ws.bound(blockIdx.x);
+    const unsigned long long w1 = p.ws.bound(blockIdx.x + 1);
+    const unsigned n_jtiles = p.ws.n_jtiles;
+
+    // j-tile ring fed by thread 0, two tiles ahead (as in direct_f32_kernel above)
+    constexpr unsigned AHEAD = STAGES - 2;
+    const unsigned n_tiles = (unsigned)(w1 - w0);
+    const unsigned tile0 = (unsigned)(w0 % n_jtiles);
+    auto global_tile = [&](unsigned t) {
+        const unsigned g = p.jt_begin + t;
+        return g >= p.jt_total ? g - p.jt_total : g;
+    };
+    auto issue_tile = [&](unsigned k) {
+        const unsigned s = k % STAGES;
+        if (k >= STAGES) mbar_wait(&empty_bar[s], ((k / STAGES) - 1u) & 1u);
+        const unsigned first = global_tile((tile0 + k) % n_jtiles) * TQ;
+        const unsigned nq = min((unsigned)TQ, p.n_units - first);
+        const unsigned bytes = nq * 64u;
+        mbar_arrive_expect_tx(&full_bar[s], bytes);
+        tma_load_1d(&tiles[s][0], q + (size_t)first * 4, bytes, &full_bar[s]);
+    };
+    if (threadIdx.x == 0)
+        for (unsigned k = 0; k < AHEAD && k < n_tiles; ++k) issue_tile(k);
+
+    const int tidc = threadIdx.x;
+    const float dtf = (float)p.dt;
+    const float e2s = (float)p.eps2;
+    unsigned stage = 0, phase = 0, kt = 0;
+
+    unsigned long long w = w0;
+    while (w < w1) {
+        const unsigned ib = (unsigned)(w / n_jtiles);
+        const unsigned t0 = (unsigned)(w - (unsigned long long)ib * n_jtiles);
+        const unsigned cnt = (unsigned)min((unsigned long long)(n_jtiles - t0), w1 - w);
+        // the thread's QPT quads; pairs 2u, 2u+1 are (x0,x1), (x2,x3) of quad u
+        unsigned iq[QPT];
+        bool valid[QPT];
+        float2 xi[NP], yi[NP], zi[NP];
+#pragma unroll
+        for (int u = 0; u < QPT; ++u) {
+            iq[u] = p.i_begin + ib * QPB + u * NT + tidc; // coalesced: quad u of thread t
+            valid[u] = iq[u] < p.i_end;
+            const unsigned iqc = valid[u] ? iq[u] : p.i_begin;
+            const float4 XI = q[(size_t)iqc * 4 + 0];
+            const float4 YI = q[(size_t)iqc * 4 + 1];
+            const float4 ZI = q[(size_t)iqc * 4 + 2];
+            xi[2 * u] = make_float2(XI.x, XI.y); xi[2 * u + 1] = make_float2(XI.z, XI.w);
+            yi[2 * u] = make_float2(YI.x, YI.y); yi[2 * u + 1] = make_float2(YI.z, YI.w);
+            zi[2 * u] = make_float2(ZI.x, ZI.y); zi[2 * u + 1] = make_float2(ZI.z, ZI.w);
+        }
+#pragma unroll
+        for (int c = 0; c < 6 * NP; ++c) dacc[c][tidc] = 0.0;
+
+        for (unsigned k = 0; k < cnt; ++k) {
+            const unsigned first = global_tile(t0 + k) * TQ;
+            const int nq = (int)min((unsigned)TQ, p.n_units - first);
+            float2 ax[NP], ay[NP], az[NP];
+#pragma unroll
+            for (int r = 0; r < NP; ++r) ax[r] = ay[r] = az[r] = make_float2(0.f, 0.f);
+
+            if (threadIdx.x == 0 && kt + AHEAD < n_tiles) issue_tile(kt + AHEAD);
+            ++kt;
+            mbar_wait(&full_bar[stage], phase);
+            const float4 *__restrict__ tile = &tiles[stage][0];
+#pragma unroll 1
+            for (int jq = 0; jq < nq; ++jq) {
+                const float4 JX = tile[jq * 4 + 0];
+                const float4 JY = tile[jq * 4 + 1];
+                const float4 JZ = tile[jq * 4 + 2];
+                float4 JM = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (MODE != 2) JM = tile[jq * 4 + 3];
+                one_j_ipacked<MODE == 2, NP>(JX.x, JY.x, JZ.x, JM.x, xi, yi, zi, e2s, ax, ay, az);
+                one_j_ipacked<MODE == 2, NP>(JX.y, JY.y, JZ.y, JM.y, xi, yi, zi, e2s, ax, ay, az);
+                one_j_ipacked<MODE == 2, NP>(JX.z, JY.z, JZ.z, JM.z, xi, yi, zi, e2s, ax, ay, az);
+                one_j_ipacked<MODE == 2, NP>(JX.w, JY.w, JZ.w, JM.w, xi, yi, zi, e2s, ax, ay, az);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty_bar[stage]);
+            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+            // flush the tile's FP32 partials into the FP64 running sums
+#pragma unroll
+            for (int r = 0; r < NP; ++r) {
+                dacc[6 * r + 0][tidc] += (double)ax[r].x;
+                dacc[6 * r + 1][tidc] += (double)ax[r].y;
+                dacc[6 * r + 2][tidc] += (double)ay[r].x;
+                dacc[6 * r + 3][tidc] += (double)ay[r].y;
+                dacc[6 * r + 4][tidc] += (double)az[r].x;
+                dacc[6 * r + 5][tidc] += (double)az[r].y;
+            }
+        }
+        w += cnt;
+
+        // From here on one quad at a time (u): sums of quad u = pairs 2u, 2u+1.
+        // Workspace / parking layout per i-block: [slot][u][6][NT] double2 -- plane c of quad u
+        // holds (dax0,dax1),(dax2,dax3),(day0,day1),... like the j-packed kernel's per-quad planes.
+        bool do_epilogue = true;
+        unsigned nslots = 1;
+        double2 *ws = nullptr;
+        if (cnt != n_jtiles) {
+            const unsigned long long x0 = (unsigned long long)ib * n_jtiles;
+            const unsigned c_first = p.ws.owner(x0);
+            const unsigned c_last = p.ws.owner(x0 + n_jtiles - 1);
+            nslots = c_last - c_first + 1;
+            const unsigned slot = blockIdx.x - c_first;
+            ws = reinterpret_cast<double2 *>(p.workspace) + ((size_t)ib * p.max_slots) * (size_t)(QPB * 6);
+            double2 *mine = ws + (size_t)slot * (QPB * 6);
+#pragma unroll
+            for (int u = 0; u < QPT; ++u)
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    // component c of pairs 2u (bodies 0,1) and 2u+1 (bodies 2,3)
+                    mine[(u * 6 + 2 * c + 0) * NT + tidc] =
+                        make_double2(dacc[12 * u + 2 * c][tidc], dacc[12 * u + 2 * c + 1][tidc]);
+                    mine[(u * 6 + 2 * c + 1) * NT + tidc] =
+                        make_double2(dacc[12 * u + 6 + 2 * c][tidc], dacc[12 * u + 6 + 2 * c + 1][tidc]);
+                }
+            __threadfence();
+            named_sync(1, NT);
+            if (tidc == 0) {
+                const unsigned old = atomicAdd(&p.counters[ib], 1u);
+                const unsigned last = (old == nslots - 1);
+                if (last) p.counters[ib] = 0; // ready for the next launch
+                s_last = last;
+            }
+            named_sync(1, NT);
+            do_epilogue = (s_last != 0);
+            if (do_epilogue) __threadfence();
+            named_sync(1, NT); // s_last may be rewritten by the next i-block
+        }
+        if (!do_epilogue) continue;
+
+        double2 *park = (p.flags & (NB_F_PARTIAL_IN | NB_F_PARTIAL_OUT))
+                            ? reinterpret_cast<double2 *>(p.partial) + (size_t)ib * (QPB * 6)
+                            : nullptr;
+#pragma unroll
+        for (int u = 0; u < QPT; ++u) {
+            // d[c][r]: component c (x,y,z) of body r of quad u
+            double d[3][4];
+            if (cnt != n_jtiles) { // add the partial j-ranges in slot order (deterministic)
+#pragma unroll
+                for (int c = 0; c < 3; ++c) d[c][0] = d[c][1] = d[c][2] = d[c][3] = 0.0;
+                for (unsigned s = 0; s < nslots; ++s) {
+                    const double2 *src = ws + (size_t)s * (QPB * 6);
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        const double2 v0 = __ldcg(&src[(u * 6 + 2 * c + 0) * NT + tidc]);
+                        const double2 v1 = __ldcg(&src[(u * 6 + 2 * c + 1) * NT + tidc]);
+                        d[c][0] += v0.x; d[c][1] += v0.y; d[c][2] += v1.x; d[c][3] += v1.y;
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    d[c][0] = dacc[12 * u + 2 * c][tidc];
+                    d[c][1] = dacc[12 * u + 2 * c + 1][tidc];
+                    d[c][2] = dacc[12 * u + 6 + 2 * c][tidc];
+                    d[c][3] = dacc[12 * u + 6 + 2 * c + 1][tidc];
+                }
+            }
+            // multi-rank: sums parked between the own-slice and the gathered j-ranges
+            if (park) {
+                if (p.flags & NB_F_PARTIAL_IN) {
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        const double2 v0 = park[(u * 6 + 2 * c + 0) * NT + tidc];
+                        const double2 v1 = park[(u * 6 + 2 * c + 1) * NT + tidc];
+                        d[c][0] += v0.x; d[c][1] += v0.y; d[c][2] += v1.x; d[c][3] += v1.y;
+                    }
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        park[(u * 6 + 2 * c + 0) * NT + tidc] = make_double2(d[c][0], d[c][1]);
+                        park[(u * 6 + 2 * c + 1) * NT + tidc] = make_double2(d[c][2], d[c][3]);
+                    }
+                    continue; // no epilogue in a PARTIAL_OUT launch
+                }
+            }
+            if (!valid[u]) continue;
+            // ---------------- epilogue: kick2 / kick1 / drift, one HBM round trip ------
+            float a[3][4];
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+#pragma unroll
+                for (int r = 0; r < 4; ++r) a[c][r] = (float)(p.G * d[c][r]);
+            const unsigned iqu = iq[u];
+            if (p.flags & NB_F_STORE_ACC) {
+                float4 *acc = static_cast<float4 *>(p.acc);
+#pragma unroll
+                for (int c = 0; c < 3; ++c)
+                    acc[(size_t)iqu * 3 + c] = make_float4(a[c][0], a[c][1], a[c][2], a[c][3]);
+            }
+            if (p.flags & (NB_F_KICK2 | NB_F_KICK1_DRIFT)) {
+                float4 *vel = static_cast<float4 *>(p.vel);
+                float4 *qn = static_cast<float4 *>(p.q_next);
+                const float xin[3][4] = {{xi[2 * u].x, xi[2 * u].y, xi[2 * u + 1].x, xi[2 * u + 1].y},
+                                         {yi[2 * u].x, yi[2 * u].y, yi[2 * u + 1].x, yi[2 * u + 1].y},
+                                         {zi[2 * u].x, zi[2 * u].y, zi[2 * u + 1].x, zi[2 * u + 1].y}};
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const float4 V = vel[(size_t)iqu * 3 + c];
+                    float v[4] = {V.x, V.y, V.z, V.w};
+                    float x[4];
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) {
+                        const bool real = (iqu * 4u + r) < p.n_real;
+                        if (p.flags & NB_F_KICK2) v[r] = kick(v[r], a[c][r], dtf);
+                        if (p.flags & NB_F_KICK1_DRIFT) v[r] = kick(v[r], a[c][r], dtf);
+                        x[r] = (p.flags & NB_F_KICK1_DRIFT) ? drift(xin[c][r], v[r], dtf) : xin[c][r];
+                        if (!real) { v[r] = 0.f; x[r] = xin[c][r]; }
+                    }
+                    vel[(size_t)iqu * 3 + c] = make_float4(v[0], v[1], v[2], v[3]);
+                    if (p.flags & NB_F_KICK1_DRIFT)
+                        qn[(size_t)iqu * 4 + c] = make_float4(x[0], x[1], x[2], x[3]);
+                }
+            }
+        }
+    }
+}
+
 } // namespace
 
 // ------------------------------------------------------------------ host ----
@@ -396,18 +677,33 @@ void apply_geom(const DirectPlan &plan, int geom, StepParams *p)
 }
 
 namespace {
-// Size classes.  i-block = NW*128 bodies, j-tile = TQ*4 bodies, MINB resident
-// CTAs per SM asked of ptxas (register cap).
+// Size classes.  i-block = NW*32*QPT quads, j-tile = TQ*4 bodies, MINB resident CTAs per SM asked
+// of ptxas (register cap).  QPT = 0: the j-packed kernel (one quad per thread); QPT = 2: the
+// i-packed kernel (two quads = 8 i-bodies per thread, dynamic shared memory for the FP64 sums).
 // tune_flags bits 8..11 = variant + 1 forces a class (A/B runs).
 struct VariantF32 {
-    int nw, tq, minb;
+    int nw, tq, minb, qpt;
 };
-constexpr int kNumVariants = 3;
+constexpr int kNumVariants = 9;
 constexpr VariantF32 kVariants[kNumVariants] = {
-    {8, 64, 2},  // 0 large : 2 x 8 warps per SM, <=128 regs
-    {4, 64, 4},  // 1 medium: 4 x 4 warps per SM
-    {1, 16, 8},  // 2 small : latency regime
+    {8, 64, 2, 0},  // 0 j-packed, 2 x 8 warps per SM, <=128 regs (round 1's large class)
+    {4, 64, 4, 0},  // 1 medium: 4 x 4 warps per SM
+    {1, 16, 8, 0},  // 2 small : latency regime
+    {16, 64, 1, 2}, // 3 i-packed 8i, 1 x 16 warps, <=128 regs
+    {12, 64, 1, 2}, // 4 i-packed 8i, 1 x 12 warps, <=168 regs
+    {8, 64, 2, 2},  // 5 i-packed 8i, 2 x 8 warps, <=128 regs
+    {8, 64, 1, 2},  // 6 i-packed 8i, 1 x 8 warps, <=255 regs
+    {8, 64, 1, 3},  // 7 i-packed 12i, 1 x 8 warps, <=255 regs
+    {4, 64, 2, 2},  // 8 i-packed 8i, 2 x 4 warps, <=255 regs
 };
+#ifndef NB_F32_LARGE_VARIANT
+#define NB_F32_LARGE_VARIANT 6
+#endif
+
+constexpr size_t ip_smem_bytes(int nw, int tq, int qpt)
+{
+    return (size_t)STAGES * tq * 64 + (size_t)12 * qpt * nw * 32 * sizeof(double);
+}
 
 template <int NW, int TQ, int MINB>
 cudaError_t launch_variant(const DirectPlan &plan, const StepParams &p, int mode,
@@ -434,6 +730,36 @@ int occupancy_variant(bool packed)
             &n, direct_f32_kernel<NW, TQ, 0, MINB>, NW * 32, 0);
     return n;
 }
+
+// i-packed kernels: more than 48 KB of dynamic shared memory, opted into once per device
+template <int NW, int TQ, int MINB, int QPT>
+cudaError_t prepare_ip()
+{
+    const int bytes = (int)ip_smem_bytes(NW, TQ, QPT);
+    cudaError_t e = cudaFuncSetAttribute(direct_f32_ip_kernel<NW, TQ, 1, MINB, QPT>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(direct_f32_ip_kernel<NW, TQ, 2, MINB, QPT>,
+                                cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+template <int NW, int TQ, int MINB, int QPT>
+int occupancy_ip()
+{
+    int n = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, direct_f32_ip_kernel<NW, TQ, 1, MINB, QPT>, NW * 32,
+                                                  ip_smem_bytes(NW, TQ, QPT));
+    return n;
+}
+template <int NW, int TQ, int MINB, int QPT>
+cudaError_t launch_ip(const DirectPlan &plan, const StepParams &p, int mode, cudaStream_t stream)
+{
+    const size_t smem = ip_smem_bytes(NW, TQ, QPT);
+    if (mode == 2)
+        direct_f32_ip_kernel<NW, TQ, 2, MINB, QPT><<<p.ws.n_ctas, plan.block, smem, stream>>>(p);
+    else
+        direct_f32_ip_kernel<NW, TQ, 1, MINB, QPT><<<p.ws.n_ctas, plan.block, smem, stream>>>(p);
+    return cudaGetLastError();
+}
 } // namespace
 
 cudaError_t plan_direct_f32(DirectPlan *plan, const SliceGeom &sg, int sm_count, int ctas_per_sm,
@@ -445,26 +771,36 @@ cudaError_t plan_direct_f32(DirectPlan *plan, const SliceGeom &sg, int sm_count,
     // bodies and still wants the large class.  Measured on B200 (tools/probe_perf.py): large wins
     // from 50k^2 up (2.42e12/s vs 2.32 medium, 2.23 small), small below 20k^2 (2.03 vs 1.93).
     const double work = (double)slice_bodies * (double)n_units * 4.0;
-    int v = work >= 9.0e8 ? 0 : 2;
+    const bool packed = !(tune_flags & 1);
+    int v = work >= 9.0e8 ? (packed ? NB_F32_LARGE_VARIANT : 0) : 2;
     const int forced = (tune_flags >> 8) & 0xf;
     if (forced >= 1 && forced <= kNumVariants) v = forced - 1;
+    if (!packed && kVariants[v].qpt) v = 0; // the scalar A/B twin exists in the j-packed kernel only
     const VariantF32 &k = kVariants[v];
+    const unsigned qpt = k.qpt ? (unsigned)k.qpt : 1u;
     plan->precision = 1;
     plan->variant = v;
-    plan->units_per_iblock = (unsigned)k.nw * 32u;
+    plan->units_per_iblock = (unsigned)k.nw * 32u * qpt;
     plan->units_per_tile = (unsigned)k.tq;
     plan->n_iblocks = (slice_units + plan->units_per_iblock - 1) / plan->units_per_iblock;
     plan->n_jtiles = (n_units + plan->units_per_tile - 1) / plan->units_per_tile;
     plan->block = (unsigned)k.nw * 32u;
     plan->slot_doubles = (size_t)plan->units_per_iblock * 12;
-    const bool packed = !(tune_flags & 1);
     int occ = 0;
+    cudaError_t err = cudaSuccess;
     switch (v) {
     case 0: occ = occupancy_variant<8, 64, 2>(packed); break;
     case 1: occ = occupancy_variant<4, 64, 4>(packed); break;
-    default: occ = occupancy_variant<1, 16, 8>(packed); break;
+    case 2: occ = occupancy_variant<1, 16, 8>(packed); break;
+    case 3: err = prepare_ip<16, 64, 1, 2>(); occ = occupancy_ip<16, 64, 1, 2>(); break;
+    case 4: err = prepare_ip<12, 64, 1, 2>(); occ = occupancy_ip<12, 64, 1, 2>(); break;
+    case 5: err = prepare_ip<8, 64, 2, 2>(); occ = occupancy_ip<8, 64, 2, 2>(); break;
+    case 6: err = prepare_ip<8, 64, 1, 2>(); occ = occupancy_ip<8, 64, 1, 2>(); break;
+    case 7: err = prepare_ip<8, 64, 1, 3>(); occ = occupancy_ip<8, 64, 1, 3>(); break;
+    default: err = prepare_ip<4, 64, 2, 2>(); occ = occupancy_ip<4, 64, 2, 2>(); break;
     }
-    cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) return err;
+    err = cudaGetLastError();
     if (err != cudaSuccess) return err;
     if (occ < 1) occ = 1;
     int per_sm = ctas_per_sm > 0 ? ctas_per_sm : k.minb;
@@ -483,7 +819,13 @@ cudaError_t launch_direct_f32(const DirectPlan &plan, int geom, StepParams p, in
     switch (plan.variant) {
     case 0: return launch_variant<8, 64, 2>(plan, p, mode, stream);
     case 1: return launch_variant<4, 64, 4>(plan, p, mode, stream);
-    default: return launch_variant<1, 16, 8>(plan, p, mode, stream);
+    case 2: return launch_variant<1, 16, 8>(plan, p, mode, stream);
+    case 3: return launch_ip<16, 64, 1, 2>(plan, p, mode, stream);
+    case 4: return launch_ip<12, 64, 1, 2>(plan, p, mode, stream);
+    case 5: return launch_ip<8, 64, 2, 2>(plan, p, mode, stream);
+    case 6: return launch_ip<8, 64, 1, 2>(plan, p, mode, stream);
+    case 7: return launch_ip<8, 64, 1, 3>(plan, p, mode, stream);
+    default: return launch_ip<4, 64, 2, 2>(plan, p, mode, stream);
     }
 }
 

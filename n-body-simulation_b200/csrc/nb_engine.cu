@@ -120,6 +120,11 @@ struct nb_engine {
     cudaStream_t comm_stream = nullptr; // NCCL collectives (world > 1)
     cudaEvent_t ev_compute = nullptr, ev_gather = nullptr; // hand-offs between the two
     bool gather_pending = false; // an all-gather is in flight on comm_stream
+    // Barnes-Hut, world > 1: the sort is cut along the rank slices (bh_slice_max / bh_slice_sort /
+    // bh_finish); after a drift the ranks' cube maxima and the positions are in flight
+    bool bh_pipe = false, bh_pipe_pending = false;
+    cudaEvent_t ev_max = nullptr, ev_runs = nullptr;
+    int bh_emulate_runs = 0;
     bool step_ended_in_gather = false;
     cudaEvent_t ev_step0 = nullptr, ev_step1 = nullptr, ev_f0 = nullptr, ev_f1 = nullptr;
     bool have_step_ev = false, have_force_ev = false;
@@ -154,6 +159,7 @@ struct nb_engine {
     struct BhGraph {
         int cur;
         unsigned flags;
+        bool pipe;
         cudaGraphExec_t exec;
         unsigned launches;
     };
@@ -194,6 +200,20 @@ int all_gather_units(nb_engine *e, void *buf, size_t unit_bytes)
 {
     return all_gather_bytes(e, buf, (size_t)e->slice_units * unit_bytes);
 }
+// in-place all-gather on the side stream behind everything enqueued on the compute stream so
+// far; `done` (optional) is recorded behind it.  Does not touch gather_pending / ev_gather.
+int comm_all_gather(nb_engine *e, void *buf, size_t bytes, cudaEvent_t done)
+{
+    if (e->cfg.world <= 1) return NB_OK;
+    const char *send = (const char *)buf + (size_t)e->cfg.rank * bytes;
+    NB_CUDA(cudaEventRecord(e->ev_compute, e->stream));
+    NB_CUDA(cudaStreamWaitEvent(e->comm_stream, e->ev_compute, 0));
+    NB_NCCL(g_nccl.AllGather(send, buf, bytes, /*ncclInt8*/ 0, e->comm, e->comm_stream));
+    if (done) NB_CUDA(cudaEventRecord(done, e->comm_stream));
+    e->st.collectives++;
+    return NB_OK;
+}
+
 // rank r contributes bytes [r*bytes, (r+1)*bytes) of buf
 int all_gather_bytes(nb_engine *e, void *buf, size_t bytes)
 {
@@ -206,6 +226,27 @@ int all_gather_bytes(nb_engine *e, void *buf, size_t bytes)
     e->gather_pending = true;
     e->step_ended_in_gather = false; // nb_step sets it again for the gather that ends a step
     e->st.collectives++;
+    return NB_OK;
+}
+
+// After a drift wrote the own slice of q[cur ^ 1]: re-assemble everybody's positions there and
+// swap the buffers.  Barnes-Hut (pipe): the cube needs the maximum |coord| over ALL bodies before
+// any key can be computed, so every rank reduces its own slice first and those W doubles travel
+// ahead of the positions; the keys and the sort of the own slice then run under the big exchange.
+int exchange_positions(nb_engine *e)
+{
+    int rc;
+    void *qn = e->q[e->cur ^ 1];
+    if (e->bh_pipe) {
+        unsigned nl = 0;
+        NB_CUDA(bh_slice_max(&e->tree, static_cast<const double4 *>(qn), (unsigned)e->n,
+                             (unsigned)e->cfg.rank, e->slice_units, e->stream, &nl));
+        e->st.kernel_launches += nl;
+        if ((rc = comm_all_gather(e, e->tree.bbox_parts, sizeof(double), e->ev_max))) return rc;
+        e->bh_pipe_pending = true;
+    }
+    if ((rc = all_gather_units(e, qn, e->unit_bytes))) return rc;
+    e->cur ^= 1;
     return NB_OK;
 }
 
@@ -245,8 +286,10 @@ int launch_force(nb_engine *e, unsigned flags)
     NB_CUDA(cudaEventRecord(e->ev_f0, e->stream));
     int rc;
     if (e->bh) {
-        // the tree is built from everybody's positions: no own-slice head start here
-        if ((rc = wait_gather(e))) return rc;
+        const bool pipe = e->bh_pipe_pending;
+        // the tree is built from everybody's positions; what a rank can do before they land is
+        // the keys and the sort of its own slice (pipe), once every rank's cube maximum is in
+        if (!pipe && (rc = wait_gather(e))) return rc;
         BhParams bp;
         bp.q_cur = static_cast<const double4 *>(p.q_cur);
         bp.q_next = static_cast<double4 *>(p.q_next);
@@ -259,13 +302,29 @@ int launch_force(nb_engine *e, unsigned flags)
         bp.dt = p.dt; bp.eps2 = p.eps2; bp.G = p.G; bp.theta = e->cfg.theta;
         bp.count_visits = e->count_visits ? 1 : 0;
         bp.time_stages = e->bh_graphs_off ? 1 : 0;
+        bp.emulate_runs = e->bh_emulate_runs;
         unsigned nl = 0;
         bool done = false;
+        const unsigned per = e->slice_units, wr = (unsigned)e->cfg.world, rk = (unsigned)e->cfg.rank;
+        if (pipe) {
+            NB_CUDA(cudaStreamWaitEvent(e->stream, e->ev_max, 0));
+            NB_CUDA(bh_slice_sort(&e->tree, bp, rk, wr, per, e->stream, &nl));
+            // the sorted runs follow the positions on the side stream
+            if ((rc = comm_all_gather(e, e->tree.key[0], (size_t)per * sizeof(uint64_t), nullptr))) return rc;
+            if ((rc = comm_all_gather(e, e->tree.val[0], (size_t)per * sizeof(unsigned), e->ev_runs))) return rc;
+            NB_CUDA(cudaStreamWaitEvent(e->stream, e->ev_runs, 0));
+            if ((rc = wait_gather(e))) return rc; // the positions went first on that stream
+            e->bh_pipe_pending = false;
+        }
+        auto evaluate = [&](unsigned *count) -> cudaError_t {
+            return pipe ? bh_finish(&e->tree, bp, wr, per, e->stream, count)
+                        : bh_evaluate(&e->tree, bp, e->stream, count);
+        };
         if (!e->bh_graphs_off) {
             for (const nb_engine::BhGraph &g : e->bh_graphs)
-                if (g.cur == e->cur && g.flags == flags) {
+                if (g.cur == e->cur && g.flags == flags && g.pipe == pipe) {
                     NB_CUDA(cudaGraphLaunch(g.exec, e->stream));
-                    nl = g.launches;
+                    nl += g.launches;
                     done = true;
                     break;
                 }
@@ -275,25 +334,26 @@ int launch_force(nb_engine *e, unsigned flags)
                 cudaGraph_t graph = nullptr;
                 cudaGraphExec_t exec = nullptr;
                 cudaError_t ce = cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal);
+                unsigned gl = 0;
                 if (ce == cudaSuccess) {
-                    ce = bh_evaluate(&e->tree, bp, e->stream, &nl);
+                    ce = evaluate(&gl);
                     const cudaError_t ee = cudaStreamEndCapture(e->stream, &graph);
                     if (ce == cudaSuccess) ce = ee;
                 }
                 if (ce == cudaSuccess) ce = cudaGraphInstantiate(&exec, graph, 0);
                 if (graph) cudaGraphDestroy(graph);
                 if (ce == cudaSuccess) {
-                    e->bh_graphs.push_back({e->cur, flags, exec, nl});
+                    e->bh_graphs.push_back({e->cur, flags, pipe, exec, gl});
                     NB_CUDA(cudaGraphLaunch(exec, e->stream));
+                    nl += gl;
                     done = true;
                 } else { // no graphs on this engine: fall back to plain launches, loudly in the stats
                     cudaGetLastError();
                     e->bh_graphs_off = true;
-                    nl = 0;
                 }
             }
         }
-        if (!done) NB_CUDA(bh_evaluate(&e->tree, bp, e->stream, &nl));
+        if (!done) NB_CUDA(evaluate(&nl));
         e->st.kernel_launches += nl;
     } else if (e->gather_pending && e->plan.can_split && !(e->cfg.tune_flags & NB_TUNE_NO_OVERLAP)) {
         // positions of the other ranks are still in flight: start on the own slice
@@ -316,9 +376,8 @@ int launch_force(nb_engine *e, unsigned flags)
                               (unsigned long long)e->n_units * e->unit_bodies;
     if (flags & (NB_F_KICK2 | NB_F_KICK1_DRIFT)) e->vel_complete = (e->cfg.world <= 1);
     if (flags & NB_F_KICK1_DRIFT) {
-        int rc = all_gather_units(e, e->q[e->cur ^ 1], e->unit_bytes);
+        int rc = exchange_positions(e);
         if (rc) return rc;
-        e->cur ^= 1;
     }
     return NB_OK;
 }
@@ -473,6 +532,7 @@ int upload(nb_engine *e, const double *pos, const double *vel, bool sliced)
     e->cur = 0;
     e->state = SYNCED_NOACC;
     e->vel_complete = true;
+    e->bh_pipe_pending = false; // all positions are local again: the next evaluation sorts them itself
     e->st.steps_done = 0;
     return NB_OK;
 }
@@ -551,6 +611,7 @@ void nb_free(nb_engine *e)
     for (void *b : bufs)
         if (b) cudaFree(b);
     cudaEvent_t evs[] = {e->ev_step0, e->ev_step1, e->ev_f0, e->ev_f1, e->ev_compute, e->ev_gather,
+                         e->ev_max, e->ev_runs,
                          e->ev_frame_ready[0], e->ev_frame_ready[1], e->ev_frame_done[0],
                          e->ev_frame_done[1]};
     for (cudaEvent_t ev : evs)
@@ -582,6 +643,8 @@ static int init_impl(nb_engine *e, const double *pos, const double *vel)
         NB_CUDA(cudaStreamCreateWithFlags(&e->comm_stream, cudaStreamNonBlocking));
         NB_CUDA(cudaEventCreateWithFlags(&e->ev_compute, cudaEventDisableTiming));
         NB_CUDA(cudaEventCreate(&e->ev_gather)); // timed: a step ends when its all-gather landed
+        NB_CUDA(cudaEventCreateWithFlags(&e->ev_max, cudaEventDisableTiming));
+        NB_CUDA(cudaEventCreateWithFlags(&e->ev_runs, cudaEventDisableTiming));
     }
 
     const bool f32 = c.precision == NB_PREC_FP32;
@@ -630,7 +693,17 @@ static int init_impl(nb_engine *e, const double *pos, const double *vel)
         set_err("nb_init", "too many bodies for the Barnes-Hut node ids (27 bits)");
         return NB_E_INVALID;
     }
-    if (e->bh) NB_CUDA(bh_alloc(&e->tree, (unsigned)e->n));
+    e->bh_pipe = e->bh && c.world > 1 && e->n > 0 && !(c.tune_flags & NB_TUNE_REPLICATED_SORT);
+    e->bh_emulate_runs = (e->bh && c.world == 1) ? ((c.tune_flags >> 24) & 0xf) : 0;
+    if (e->bh) {
+        size_t n_keys = e->n;
+        if (c.world > 1) n_keys = (size_t)e->slice_units * c.world;
+        if (e->bh_emulate_runs > 1) {
+            const size_t per = ((e->n + e->bh_emulate_runs - 1) / e->bh_emulate_runs + 127) / 128 * 128;
+            n_keys = per * e->bh_emulate_runs;
+        }
+        NB_CUDA(bh_alloc(&e->tree, (unsigned)e->n, (unsigned)n_keys, (unsigned)c.world));
+    }
     if (e->bh && e->n > 1 && !(c.tune_flags & NB_TUNE_NO_REORDER)) {
         NB_CUDA(cudaMalloc(&e->user_of, e->n * sizeof(unsigned)));
         NB_CUDA(cudaMalloc(&e->order_tmp, e->n * 4 * sizeof(double)));
@@ -761,9 +834,8 @@ int nb_step(nb_engine *e, int n_steps)
                               e->i_begin, e->i_end, (unsigned)e->n, e->cfg.dt, e->stream));
             e->st.kernel_launches++;
             e->vel_complete = (e->cfg.world <= 1);
-            rc = all_gather_units(e, e->q[e->cur ^ 1], e->unit_bytes);
+            rc = exchange_positions(e);
             if (rc) return rc;
-            e->cur ^= 1;
         } else if (e->state == SYNCED_NOACC) {
             rc = launch_force(e, NB_F_KICK1_DRIFT);
             if (rc) return rc;
@@ -978,7 +1050,7 @@ int nb_tree_stats(nb_engine *e, nb_tree_info *out)
     out->interactions = bs.interactions;
     out->node_visits = bs.visits;
     out->child_tests = bs.child_tests;
-    for (int k = 0; k < 6; ++k) out->stage_ms[k] = bs.stage_ms[k];
+    for (int k = 0; k < 8; ++k) out->stage_ms[k] = k < BH_STAGES ? bs.stage_ms[k] : 0.0;
     out->pool_overflow = (int)bs.pool_overflow;
     out->stack_overflow = (int)bs.stack_overflow;
     if (bs.pool_overflow || bs.stack_overflow) {

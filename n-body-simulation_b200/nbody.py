@@ -23,6 +23,8 @@ TUNE_SCALAR_FP32, TUNE_NO_SPLIT, TUNE_NO_OVERLAP, TUNE_COUNT_VISITS, TUNE_NO_UNI
 TUNE_NO_REORDER = 32
 TUNE_NO_INTERLEAVE = 64
 TUNE_NO_GRAPH = 128
+TUNE_REPLICATED_SORT = 1 << 28
+TUNE_EMULATE_RUNS_SHIFT = 24  # Barnes-Hut on one rank: sort as (flags >> 24 & 15) slices + merge
 SLICE_ALIGN = {PREC_FP32: 64, PREC_FP64: 128}  # units; nb_direct.cuh kSliceAlign*
 
 # every symbol include/nbody_engine.h declares
@@ -56,7 +58,7 @@ class NbTreeInfo(C.Structure):
     _fields_ = [("nodes", C.c_uint), ("depth", C.c_uint), ("root_border", C.c_double),
                 ("interactions", C.c_ulonglong), ("node_visits", C.c_ulonglong),
                 ("pool_overflow", C.c_int), ("stack_overflow", C.c_int),
-                ("child_tests", C.c_ulonglong), ("stage_ms", C.c_double * 6)]
+                ("child_tests", C.c_ulonglong), ("stage_ms", C.c_double * 8)]
 
 
 class NbodyError(RuntimeError):

@@ -299,3 +299,35 @@ def test_bh_graph_replay_equals_plain_launches(nb):
             res.append((out, st.kernel_launches, st.force_launches))
     assert all(np.array_equal(a, b) for a, b in zip(res[0][0], res[1][0]))
     assert res[0][1:] == res[1][1:]
+
+
+@pytest.mark.parametrize("runs", [2, 3, 5, 8])
+@pytest.mark.parametrize("n", [2, 100, 1000, 10_000, 50_000])
+def test_bh_slice_sort_and_merge_equals_full_sort(nb, runs, n):
+    """Multi-rank engines sort the Morton keys of their own slice and merge the all-gathered runs
+    (merge path, ties to the left run) instead of radix-sorting all keys on every rank.  The
+    single-rank rehearsal (tune_flags bits 24..27 = number of slices) must reproduce the full
+    sort's sequence, hence the same tree and bit-identical results -- including equal keys
+    (coincident bodies) and runs that are partly or wholly padding."""
+    g = golden("10k_bodies_g1")
+    rng = np.random.default_rng(n + runs)
+    if n <= 10_000:
+        pm, vel = g["pos_xyzm"][:n].copy(), g["vel"][:n].copy()
+    else:
+        pm = np.concatenate([rng.standard_normal((n, 3)), rng.uniform(0.1, 1.0, (n, 1))], axis=1)
+        vel = rng.standard_normal((n, 3))
+    if n >= 100:
+        pm[n // 2, :3] = pm[3, :3]          # coincident pair: equal keys in different runs
+        pm[n - 1, :3] = pm[3, :3]
+    res = []
+    for flags in (0, runs << nb.TUNE_EMULATE_RUNS_SHIFT, (runs << nb.TUNE_EMULATE_RUNS_SHIFT) | nb.TUNE_NO_GRAPH):
+        with bh_engine(nb, pm, vel, tune_flags=flags | nb.TUNE_COUNT_VISITS) as e:
+            acc = e.accelerations()
+            ti = e.tree_stats()
+            e.step(3)
+            p, v = e.gather()
+        res.append((acc, p, v, ti.nodes, ti.depth, ti.interactions, ti.node_visits))
+    for other in res[1:]:
+        for a, b in zip(res[0][:3], other[:3]):
+            assert np.array_equal(a, b)
+        assert res[0][3:] == other[3:]

@@ -236,6 +236,43 @@ def test_all_size_classes(nb, variant, prec):
     assert rel_err(acc, g["acc0"]).max() <= (1e-12 if prec == "fp64" else 1e-5)
 
 
+@pytest.mark.parametrize("variant", [4, 5, 6, 7])
+@pytest.mark.parametrize("masses", ["equal", "spread"])
+@pytest.mark.parametrize("n", [5, 1000, 10_000, 33_000])
+def test_fp32_ipacked_size_classes(nb, oracle_lib, variant, masses, n):
+    """The i-packed FP32 kernels (8 i-bodies per thread; 1x16, 1x12, 2x8, 1x8 warps per SM), forced
+    through tune_flags on inputs from a few bodies (one ragged i-block) to several i-blocks whose
+    j-ranges are cut between CTAs: accelerations against the oracle, 3 leapfrog steps against the
+    j-packed kernel (variant 1), equal and general masses."""
+    import oracle as O
+    g = golden("10k_bodies_g1")
+    rng = np.random.default_rng(n)
+    if n <= 10_000:
+        pm, vel = g["pos_xyzm"][:n].copy(), g["vel"][:n].copy()
+    else:
+        pm = np.concatenate([rng.standard_normal((n, 3)), np.full((n, 1), 0.2)], axis=1)
+        vel = rng.standard_normal((n, 3))
+    if masses == "spread":
+        pm[:, 3] = rng.uniform(0.1, 0.3, n)
+    pm = pm.astype(np.float32).astype(np.float64)
+    vel = vel.astype(np.float32).astype(np.float64)
+    with nb.Engine(pm, vel, precision=nb.PREC_FP32, tune_flags=variant << 8) as e:
+        acc = e.accelerations()
+        e.step(3)
+        p, v = e.gather()
+        assert e.stats().uniform_mass == (1 if masses == "equal" else 0)
+    with nb.Engine(pm, vel, precision=nb.PREC_FP32, tune_flags=1 << 8) as e:
+        acc1 = e.accelerations()
+        e.step(3)
+        p1, v1 = e.gather()
+    if n <= 10_000:
+        ref = O.acceleration(oracle_lib, pm, "orc_acceleration_mt", 8)
+        assert rel_err(acc, ref).max() <= 1e-5
+    assert rel_err(acc, acc1).max() <= 2e-6
+    assert rel_err(p, p1).max() <= 2e-5 and rel_err(v, v1).max() <= 2e-5
+    assert np.array_equal(p[:, 3], pm[:, 3])
+
+
 # -------------------------------------------- size-independent properties ---
 @pytest.mark.parametrize("prec,n,masses", [("fp32", 200_000, "spread"), ("fp64", 60_000, "spread"),
                                            ("fp32", 1_000_000, "equal"),    # BASELINE config 3 (bench)

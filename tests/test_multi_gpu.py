@@ -153,7 +153,7 @@ def test_overlap_and_serial_exchange_agree(nb):
     assert rel_err(a[0][0], b[0][0]).max() <= 1e-11 and rel_err(a[0][1], b[0][1]).max() <= 1e-11
 
 
-@pytest.mark.parametrize("world", [2, 8])
+@pytest.mark.parametrize("world", [2, 3, 4, 8])
 def test_barnes_hut_ranks_bitwise(nb, world):
     """Barnes-Hut over W ranks: every rank builds the same tree from the gathered positions and
     walks the bodies of its own slice; a body's interaction list does not depend on who walks
@@ -173,6 +173,9 @@ def test_barnes_hut_ranks_bitwise(nb, world):
         return acc, p, v
 
     for acc, p, v in run_ranks(nb, world, fn, g["pos_xyzm"], g["vel"], **kw):
+        assert np.array_equal(acc, a1) and np.array_equal(p, p1) and np.array_equal(v, v1)
+    # round 1's replicated sort (every rank sorts all keys) gives the same bits
+    for acc, p, v in run_ranks(nb, world, fn, g["pos_xyzm"], g["vel"], tune_flags=nb.TUNE_REPLICATED_SORT, **kw):
         assert np.array_equal(acc, a1) and np.array_equal(p, p1) and np.array_equal(v, v1)
 
 
