@@ -518,21 +518,27 @@ def direct_record(ctx, what, pm, vel, prec, steps, warmup, tune_flags=0, target_
             steps = ctx.steps_for(eng, target_s, 5, 200)
         dev_ms, force_ms, launches, clocks = ctx.timed(eng, steps, warmup)
         uni = eng.stats().uniform_mass
+        variant = eng.stats().kernel_variant
     if ctx.rank != 0:
         return None
     return {"workload": what, "bodies": n, "precision": "fp32" if prec == nb.PREC_FP32 else "fp64",
             "n_gpus": ctx.world, "steps": steps, "warmup": warmup, "ms_per_step": dev_ms / steps,
             "value": steps * float(n) * n / (dev_ms * 1e-3), "unit": "interactions/s",
             "steps_per_s": steps / (dev_ms * 1e-3), "gpu_launches": launches, "clocks": clocks,
-            "kernel": kernel_name(nb, prec, uni),
+            "kernel": kernel_name(nb, prec, uni, variant),
             "roofline": direct_roofline(nb, prec, uni, my_rows, st0.n_padded, force_ms / steps, clocks)}
 
 
-def kernel_name(nb, prec, uniform_mass):
+def kernel_name(nb, prec, uniform_mass, variant=None):
     if prec != nb.PREC_FP32:
-        return "fp64: 16 FP64-pipe ops + 1 MUFU per interaction"
-    return ("packed f32x2, equal masses: m_j hoisted out of the loop, 11 FMA-pipe ops + 1 MUFU per interaction"
-            if uniform_mass else "packed f32x2, general masses: 12 FMA-pipe ops + 1 MUFU per interaction")
+        return "direct_f64_kernel (variant %s): 16 FP64-pipe ops + 1 MUFU per interaction" % variant
+    # nb_direct_f32.cu kVariants: 0..2 pack two j-bodies per register pair (direct_f32_kernel),
+    # 3.. pack two i-bodies and take j as a broadcast scalar operand (direct_f32_ip_kernel)
+    name = "direct_f32_kernel, j-packed f32x2" if variant is not None and variant < 3 else \
+           "direct_f32_ip_kernel, i-packed f32x2 (8 i-bodies per thread, j broadcast from LDS.128)"
+    return name + (" (variant %s), equal masses: m_j hoisted, 11 FMA-pipe ops + 1 MUFU per interaction" % variant
+                   if uniform_mass else
+                   " (variant %s), general masses: 12 FMA-pipe ops + 1 MUFU per interaction" % variant)
 
 
 def e2e_loop(ctx, eng, pm, vel, reps):
@@ -888,7 +894,7 @@ def run_gpu_arm(args):
                              "collectives": int(stb.collectives)},
             "roofline": roof,
             "grid": st0.grid, "block": st0.block,
-            "kernel": kernel_name(nb, prec, uni),
+            "kernel": kernel_name(nb, prec, uni, st0.kernel_variant),
             "parity": parity,
             "configs": configs,
         }

@@ -103,6 +103,8 @@ typedef struct nb_stats {
     unsigned long long collectives;       /* all-gathers issued since nb_init (world > 1) */
     unsigned long long split_evaluations; /* force evaluations issued as own-slice + gathered launches */
     int uniform_mass; /* 1: FP32 direct kernel runs with the mass multiply hoisted (all masses equal) */
+    int kernel_variant; /* direct sum: index of the size class the plan chose (FP32: 0..2 j-packed,
+                         * 3..8 i-packed, nb_direct_f32.cu; FP64: nb_direct_f64.cu); -1 for Barnes-Hut */
 } nb_stats;
 
 /* Fills cfg with the reference's constants: FP64, direct, eps2 = 0.01, G = 1,

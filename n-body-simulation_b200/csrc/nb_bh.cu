@@ -442,7 +442,16 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
         // dist^2 + eps2 in one FMA chain: within rounding of the reference's mul/add form
         // (:101-104, :172), which moves an accept/open decision only at the very edge of THETA
         const double r2 = fma(dz, dz, fma(dy, dy, fma(dx, dx, eps2)));
-        const bool take = mine & (thr < r2) & (ent != (int)k); // no short circuit
+#ifdef NB_BH_INT_THRESHOLD
+        // thr < r2 on the bit patterns: r2 > 0 and finite, thr is -1 (bodies), a positive number,
+        // +inf (THETA = 0) or NaN (a cube of size 0: never accept) -- as signed 64-bit integers
+        // these order exactly like the doubles (NaN's pattern is above +inf: "not below", as for the
+        // doubles), and the compare leaves the FP64 pipe
+        const bool far = __double_as_longlong(thr) < __double_as_longlong(r2);
+#else
+        const bool far = thr < r2;
+#endif
+        const bool take = mine & far & (ent != (int)k); // no short circuit
         const double s0 = bh_inv_r3_times_m(r2, c.w);
         const double s = take ? s0 : 0.0; // selected after the fact: a NaN/inf of a lane that does not take it is dropped
         ax = fma(dx, s, ax); ay = fma(dy, s, ay); az = fma(dz, s, az);

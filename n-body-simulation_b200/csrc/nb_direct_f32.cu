@@ -768,11 +768,12 @@ cudaError_t plan_direct_f32(DirectPlan *plan, const SliceGeom &sg, int sm_count,
     const unsigned slice_units = sg.slice_units, n_units = sg.n_units;
     const unsigned slice_bodies = slice_units * 4u;
     // size class by work (i x j), not by slice length: a rank of an 8-GPU run owns 125k of 1M
-    // bodies and still wants the large class.  Measured on B200 (tools/probe_perf.py): large wins
-    // from 50k^2 up (2.42e12/s vs 2.32 medium, 2.23 small), small below 20k^2 (2.03 vs 1.93).
+    // bodies and still wants the large class.  Measured on B200 (tools/probe_perf.py, round 2,
+    // profiles/r2_notes.md): the i-packed large class wins from 20k^2 up (181 vs 187 us; 0.71 of
+    // the roofline at 30k^2, 0.77 at 1M^2), the small class below (10k^2: 60 vs 77 us).
     const double work = (double)slice_bodies * (double)n_units * 4.0;
     const bool packed = !(tune_flags & 1);
-    int v = work >= 9.0e8 ? (packed ? NB_F32_LARGE_VARIANT : 0) : 2;
+    int v = work >= 3.5e8 ? (packed ? NB_F32_LARGE_VARIANT : 0) : 2;
     const int forced = (tune_flags >> 8) & 0xf;
     if (forced >= 1 && forced <= kNumVariants) v = forced - 1;
     if (!packed && kVariants[v].qpt) v = 0; // the scalar A/B twin exists in the j-packed kernel only

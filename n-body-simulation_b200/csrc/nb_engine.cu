@@ -128,6 +128,7 @@ struct nb_engine {
     bool step_ended_in_gather = false;
     cudaEvent_t ev_step0 = nullptr, ev_step1 = nullptr, ev_f0 = nullptr, ev_f1 = nullptr;
     bool have_step_ev = false, have_force_ev = false;
+    bool time_force = true; // nb_step times only the last evaluation of a multi-step call
     void *q[2] = {nullptr, nullptr};
     int cur = 0;
     void *vel = nullptr, *acc = nullptr;
@@ -283,7 +284,7 @@ int launch_force(nb_engine *e, unsigned flags)
     p.eps2 = e->cfg.eps2;
     p.G = e->uniform ? e->cfg.G * e->uniform_m : e->cfg.G;
     p.uniform_mass = e->uniform ? 1u : 0u;
-    NB_CUDA(cudaEventRecord(e->ev_f0, e->stream));
+    if (e->time_force) NB_CUDA(cudaEventRecord(e->ev_f0, e->stream));
     int rc;
     if (e->bh) {
         const bool pipe = e->bh_pipe_pending;
@@ -368,8 +369,10 @@ int launch_force(nb_engine *e, unsigned flags)
         if ((rc = wait_gather(e))) return rc;
         if ((rc = launch_kernel(e, NB_GEOM_FULL, p))) return rc;
     }
-    NB_CUDA(cudaEventRecord(e->ev_f1, e->stream));
-    e->have_force_ev = true;
+    if (e->time_force) {
+        NB_CUDA(cudaEventRecord(e->ev_f1, e->stream));
+        e->have_force_ev = true;
+    }
     e->st.force_launches++;
     if (!e->bh) // direct sum: every ordered pair; Barnes-Hut counts on the device (nb_tree_stats)
         e->st.interactions += (unsigned long long)(e->i_end - e->i_begin) * e->unit_bodies *
@@ -828,7 +831,9 @@ int nb_step(nb_engine *e, int n_steps)
     int rc = set_device(e);
     if (rc) return rc;
     NB_CUDA(cudaEventRecord(e->ev_step0, e->stream));
+    struct Restore { nb_engine *e; ~Restore() { e->time_force = true; } } restore{e};
     for (int s = 0; s < n_steps; ++s) {
+        e->time_force = (s == n_steps - 1);
         if (e->state == SYNCED_ACC) {
             NB_CUDA(kickdrift(e->cfg.precision, e->q[e->cur], e->q[e->cur ^ 1], e->vel, e->acc,
                               e->i_begin, e->i_end, (unsigned)e->n, e->cfg.dt, e->stream));
@@ -1081,6 +1086,7 @@ int nb_get_stats(nb_engine *e, nb_stats *out)
         e->st.last_force_ms = ms;
     }
     e->st.uniform_mass = e->uniform ? 1 : 0;
+    e->st.kernel_variant = e->bh ? -1 : e->plan.variant;
     *out = e->st;
     return NB_OK;
 }

@@ -51,7 +51,8 @@ class NbStats(C.Structure):
                 ("grid", C.c_int), ("block", C.c_int), ("smem_bytes", C.c_int),
                 ("n", C.c_size_t), ("n_padded", C.c_size_t), ("slice_begin", C.c_size_t),
                 ("slice_end", C.c_size_t), ("collectives", C.c_ulonglong),
-                ("split_evaluations", C.c_ulonglong), ("uniform_mass", C.c_int)]
+                ("split_evaluations", C.c_ulonglong), ("uniform_mass", C.c_int),
+                ("kernel_variant", C.c_int)]
 
 
 class NbTreeInfo(C.Structure):

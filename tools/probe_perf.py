@@ -69,7 +69,9 @@ def run(spec):
         if algo == nb.ALGO_BARNES_HUT:
             ti = e.tree_stats()
             out.update({"nodes": ti.nodes, "depth": ti.depth, "interactions_per_body": ti.interactions / n,
-                        "visits_per_body": ti.node_visits / n, "launches_per_eval": None})
+                        "visits_per_body": ti.node_visits / n, "launches_per_eval": None,
+                        "stage_ms": [round(x, 4) for x in ti.stage_ms[:7]],
+                        "lib": os.path.basename(nb.nbody.LIB_PATH) if hasattr(nb, "nbody") else None})
             del out["frac_fp32_roofline_20flop_1965MHz"], out["interactions_per_s"]
     print(json.dumps(out), flush=True)
 
