@@ -653,6 +653,16 @@ def bh_record(ctx, what, pm, vel, accuracy=True, cpu_baseline=False, single_gpu_
         eng.step(2)
         steps = ctx.steps_for(eng, 1.5, 5, 200)
         dev_ms, _f, launches, clocks = ctx.timed(eng, steps, 3)
+        # the same steps as ONE nb_step(steps) call: no host sync and no L2 flush between steps
+        # (a step's working set -- positions, keys, the tree -- is larger than L2 from 1M bodies
+        # up); with world > 1 the own-slice sort of step k+1 runs under the position all-gather
+        # of step k, which the step-at-a-time loop above cannot show
+        eng.upload(pm, vel)                    # the same stretch of the system's evolution
+        eng.step(2 + 1 + 3)
+        eng.sync()
+        ctx.barrier()
+        eng.step(steps)
+        b2b_ms = ctx.reduce([eng.stats().last_step_ms], "max")[0] / steps
         wall, _chk, nin, nout = e2e_loop(ctx, eng, pm, vel, 3)
         p, v = eng.gather()
         same = ctx.ranks_agree(p, v) if ctx.world > 1 else None
@@ -674,7 +684,12 @@ def bh_record(ctx, what, pm, vel, accuracy=True, cpu_baseline=False, single_gpu_
     with ctx.engine(pm, vel, tune_flags=nb.TUNE_NO_GRAPH, **kw) as se:
         se.step(3)
         se.sync()
+        ctx.barrier()
+        se.step(1)
+        sst = se.stats()
+        plain = ctx.reduce([sst.last_force_ms, sst.last_step_ms], "max")
         stage_ms = list(se.tree_stats().stage_ms)
+    trav_min = ctx.reduce([stage_ms[6]], "min")[0]
     stage_ms = ctx.reduce(stage_ms, "max")
     # tree statistics from a counting engine (the counting walk is ~10 % slower: never timed)
     with ctx.engine(pm, vel, tune_flags=nb.TUNE_COUNT_VISITS, **kw) as ce:
@@ -695,18 +710,29 @@ def bh_record(ctx, what, pm, vel, accuracy=True, cpu_baseline=False, single_gpu_
     names = ["keys", "sort", "merge", "order", "build", "com", "traversal"]
     # algorithmic bytes per stage per rank: keys read 32 + write 12 per body; sort
     # 8 passes x 32 (world > 1: keys and sort of the OWN slice only, then ceil(log2 W) merge passes
-    # of 24 B over all keys); order 68; build 560 per cell; centre of mass 360 per cell; traversal =
-    # the cells' child blocks once (512 per cell) + 132 per own body (body, index, v in/out, x out)
+    # of 24 B over all keys); order 68; build 432 per cell (48 + the 384-byte child block);
+    # centre of mass 360 per cell; traversal = the cells' child blocks once (384 per cell) + 132
+    # per own body (body, index, v in/out, x out)
     sorted_here = own if ctx.world > 1 else n
     merge_passes = int(np.ceil(np.log2(ctx.world))) if ctx.world > 1 else 0
     stage_bytes = [44.0 * sorted_here, 256.0 * sorted_here, 24.0 * n * merge_passes, 68.0 * n,
-                   560.0 * nodes, 360.0 * nodes, 512.0 * nodes + 132.0 * own]
+                   432.0 * nodes, 360.0 * nodes, 384.0 * nodes + 132.0 * own]
+    exchange_ms = stage_ms[7] if ctx.world > 1 else None
     stage_ms = stage_ms[:7]
     stages = {}
     for nm, ms, by in zip(names, stage_ms, stage_bytes):
         gbs = by / (ms * 1e-3) / 1e9 if ms > 0 else None
         stages[nm] = {"ms": ms, "algorithmic_bytes": by, "gbs": gbs, "hbm_frac": (gbs / hp) if gbs else None}
+    if exchange_ms is not None: # not a kernel of ours: ncclAllGather of the positions (32 B/body)
+        stages["exchange"] = {"ms": exchange_ms, "algorithmic_bytes": 32.0 * n,
+                              "what": "position all-gather on the side stream, max over ranks, the "
+                                      "wait for the slowest rank's traversal included"}
     trav_ms = stage_ms[6]
+    stages["traversal"]["ms_min_over_ranks"] = trav_min
+    # the same step of the plainly launched engine as a whole: launch_force (the wait for the
+    # other ranks' cube maxima and sorted runs included) and nb_step (the position exchange too)
+    stages["whole_evaluation_plain_launches"] = {"ms": plain[0]}
+    stages["whole_step_plain_launches"] = {"ms": plain[1]}
     fp64_ach = BH_FP64_OPS_PER_TEST * 32.0 * tests_max * 2.0 / (trav_ms * 1e-3) / 1e12 if trav_ms > 0 else None
     total_stage = sum(stage_ms)
     total_bytes = sum(stage_bytes)
@@ -714,6 +740,11 @@ def bh_record(ctx, what, pm, vel, accuracy=True, cpu_baseline=False, single_gpu_
         "workload": what, "bodies": n, "precision": "fp64", "theta": 0.5, "n_gpus": ctx.world,
         "steps": steps, "ms_per_step": dev_ms / steps, "value": n * steps / (dev_ms * 1e-3),
         "unit": "body force evaluations/s", "gpu_launches": launches, "clocks": clocks,
+        "timing": "one nb_step(1) per timed iteration, L2 flushed and the host synchronised in between",
+        "back_to_back": {"ms_per_step": b2b_ms, "value": n / (b2b_ms * 1e-3),
+                         "what": "the same steps as one nb_step(%d) call (no flush: the step's "
+                                 "working set of %.0f MB exceeds the 126 MB L2)"
+                                 % (steps, (ti.nodes * 464.0 + n * 120.0) / 1e6)},
         "tree": {"nodes": nodes, "depth": ti.depth, "interactions_per_body": inter / n,
                  "visits_per_body": visits / n, "child_tests_per_warp": tests / (n / 32.0)},
         "accuracy_vs_direct": acc_stats,
@@ -722,7 +753,10 @@ def bh_record(ctx, what, pm, vel, accuracy=True, cpu_baseline=False, single_gpu_
                 "what": "nb_upload_slice + nb_step(1) + nb_gather_slice per step = 2 evaluations"},
         "roofline": {
             "bound": "fp64", "achieved": fp64_ach, "peak": FP64_PEAK_MEASURED_TFLOPS, "unit": "TFLOP/s",
-            "frac": (fp64_ach / FP64_PEAK_MEASURED_TFLOPS) if fp64_ach else None, "traffic": None,
+            "frac": (fp64_ach / FP64_PEAK_MEASURED_TFLOPS) if fp64_ach else None,
+            # traverse_kernel, 1M Plummer on one GPU: dram read 373.9 MB + write 54.2 MB per launch
+            # (profiles/r2_bh_traverse_ncu_full_before.csv); other shapes were not captured
+            "traffic": 428099072 if (n == 1_000_000 and ctx.world == 1 and "Plummer" in what) else None,
             "what": "traversal kernel (%.0f %% of the evaluation): %d FP64 warp instructions per child "
                     "record tested x 32 lanes x 2 flop, over the traversal's device time, against the "
                     "measured DFMA rate 62.2 lanes/clk/SM x 148 SM x 1965 MHz; a record costs the same "
@@ -826,39 +860,49 @@ def run_gpu_arm(args):
 
     # ---- the other BASELINE configs -----------------------------------------------------------
     configs = {}
+    only = set(args.only.split(",")) if args.only else None
+
+    def want(name):
+        return not args.no_configs and (only is None or name in only)
+
     if not args.no_configs:
         sub_steps = max(3, min(args.steps, 5))
-        pm_s = pm.copy()
-        pm_s[:, 3] = np.random.default_rng(18).uniform(0.5, 1.5, n) / n
-        configs["fp32_1M_spread"] = direct_record(
-            ctx, "synthetic %d-body Plummer sphere, masses U(0.5,1.5)/N: the general FP32 kernel" % n,
-            pm_s, vel, nb.PREC_FP32, sub_steps, 3)
-        del pm_s
+        if want("fp32_1M_spread"):
+            pm_s = pm.copy()
+            pm_s[:, 3] = np.random.default_rng(18).uniform(0.5, 1.5, n) / n
+            configs["fp32_1M_spread"] = direct_record(
+                ctx, "synthetic %d-body Plummer sphere, masses U(0.5,1.5)/N: the general FP32 kernel" % n,
+                pm_s, vel, nb.PREC_FP32, sub_steps, 3)
+            del pm_s
         pu, vu = uniform_cube(n)
-        configs["fp32_1M_uniform"] = direct_record(
-            ctx, "synthetic %d-body uniform cube U(-1,1)^3, v = 0, m = 1/N, FP32" % n,
-            pu, vu, nb.PREC_FP32, sub_steps, 3)
-        p100, v100 = fixture_like(100_000)
-        configs["fp64_100k"] = direct_record(
-            ctx, "BASELINE config 2: 100k bodies (the recipe of the reference's fixtures: numpy seed 17, "
-                 "randn, mass 0.2; tests/100k_bodies.csv itself is missing from the reference checkout), "
-                 "FP64 direct sum", p100, v100, nb.PREC_FP64, 20, 3, target_s=1.5)
+        if want("fp32_1M_uniform"):
+            configs["fp32_1M_uniform"] = direct_record(
+                ctx, "synthetic %d-body uniform cube U(-1,1)^3, v = 0, m = 1/N, FP32" % n,
+                pu, vu, nb.PREC_FP32, sub_steps, 3)
+        if want("fp64_100k"):
+            p100, v100 = fixture_like(100_000)
+            configs["fp64_100k"] = direct_record(
+                ctx, "BASELINE config 2: 100k bodies (the recipe of the reference's fixtures: numpy seed 17, "
+                     "randn, mass 0.2; tests/100k_bodies.csv itself is missing from the reference checkout), "
+                     "FP64 direct sum", p100, v100, nb.PREC_FP64, 20, 3, target_s=1.5)
         nbh = min(n, 1_000_000)
         pbh, vbh = (pm, vel) if nbh == n else plummer(nbh)
-        configs["bh_1M"] = bh_record(
-            ctx, "BASELINE config 4: synthetic %d-body Plummer sphere, Barnes-Hut THETA=0.5, FP64" % nbh,
-            pbh, vbh, accuracy=True, cpu_baseline=(world == 1 and not args.no_cpu_baseline))
-        configs["bh_1M_uniform"] = bh_record(
-            ctx, "synthetic %d-body uniform cube, Barnes-Hut THETA=0.5, FP64" % nbh,
-            pu[:nbh], vu[:nbh], accuracy=False, single_gpu_check=False)
+        if want("bh_1M"):
+            configs["bh_1M"] = bh_record(
+                ctx, "BASELINE config 4: synthetic %d-body Plummer sphere, Barnes-Hut THETA=0.5, FP64" % nbh,
+                pbh, vbh, accuracy=True, cpu_baseline=(world == 1 and not args.no_cpu_baseline))
+        if want("bh_1M_uniform"):
+            configs["bh_1M_uniform"] = bh_record(
+                ctx, "synthetic %d-body uniform cube, Barnes-Hut THETA=0.5, FP64" % nbh,
+                pu[:nbh], vu[:nbh], accuracy=False, single_gpu_check=False)
         del pu, vu
-        if world == 8 or args.bh16m:
+        if (world == 8 or args.bh16m) and want("bh_16M"):
             p16, v16 = plummer(16_000_000)
             configs["bh_16M"] = bh_record(
                 ctx, "BASELINE config 5: synthetic 16M-body Plummer sphere, Barnes-Hut THETA=0.5, FP64, "
                      "i-slices over %d GPU(s)" % world, p16, v16, accuracy=False)
             del p16, v16
-        if world == 1:
+        if world == 1 and want("small_n"):
             configs["small_n"] = small_n_record(ctx)
         for k in ("bh_1M", "bh_1M_uniform", "bh_16M"):
             if k in configs and not bh_parity_ok(configs[k]):
@@ -867,8 +911,9 @@ def run_gpu_arm(args):
     if rank == 0:
         roof = direct_roofline(nb, prec, uni, my_rows, st0.n_padded, force_ms / args.steps, clocks)
         # one ncu --set full capture of this very launch (1M bodies, FP32, one GPU):
-        # dram__bytes_read.sum + dram__bytes_write.sum (profiles/); other shapes were not captured
-        roof["traffic"] = 30671104 if (n == 1_000_000 and world == 1 and prec == nb.PREC_FP32 and uni) else None
+        # dram__bytes_read.sum + dram__bytes_write.sum (profiles/r2_direct_f32_ip_ncu_full.csv:
+        # 28.84 MB + 1.90 MB); other shapes were not captured
+        roof["traffic"] = 30742016 if (n == 1_000_000 and world == 1 and prec == nb.PREC_FP32 and uni) else None
         roof["traffic_note"] = ("bytes per launch from ncu (dram read + write); the algorithmic 64 B/body "
                                 "include the 32 MB of writes, which leave L2 only after the launch. "
                                 "The kernel is FMA-bound: HBM traffic is ~1e-4 of the time budget")
@@ -967,6 +1012,7 @@ def main():
     ap.add_argument("--tune-flags", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-configs", action="store_true", help="headline only: skip the `configs` records")
+    ap.add_argument("--only", default="", help="comma list of `configs` records to run (default: all)")
     ap.add_argument("--no-ref-gpu", action="store_true", help="skip the reference's own CUDA programs")
     ap.add_argument("--ref-gpu-bh", action="store_true",
                     help="also try the reference's barnes-hut-cuda at 1M bodies (it does not terminate on "

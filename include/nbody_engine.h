@@ -191,7 +191,9 @@ typedef struct nb_tree_info {
     unsigned long long child_tests;
     /* NB_TUNE_NO_GRAPH: device time (ms) of the stages of the last evaluation -- cube + keys,
      * radix sort (world > 1: of the own slice), merge of the ranks' sorted runs (world > 1),
-     * bodies in Morton order (+ own list), build, centre of mass, traversal; else 0 */
+     * bodies in Morton order (+ own list), build, centre of mass, traversal; else 0.
+     * [7] (world > 1, always): the last position exchange on the side stream, from the moment this
+     * rank was ready to the end of the all-gather -- waiting for the slowest rank included */
     double stage_ms[8];
 } nb_tree_info;
 int nb_tree_stats(nb_engine *e, nb_tree_info *out);

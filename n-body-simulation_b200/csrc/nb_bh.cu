@@ -361,7 +361,7 @@ __global__ void __launch_bounds__(BH_THREADS)
 // drops out of its subtree.  Each body therefore sees exactly the serial
 // reference's interaction list, in the reference's order (children 0..7,
 // depth first), and agrees with it to rounding, not just within the THETA
-// envelope.  An opened cell's child records (one 512-byte block) are fetched by
+// envelope.  An opened cell's child records (one 384-byte block) are fetched by
 // the warp in one coalesced copy and tested in one go (one memory round trip per
 // OPENED cell instead of one per visited node); only cells that some lane must
 // open go through the stack.  The sum order therefore is "a cell's accepted
@@ -405,7 +405,11 @@ __device__ __forceinline__ double bh_inv_r3_times_m(double r2, double m)
 #ifndef NB_BH_TRAV_MINB
 #define NB_BH_TRAV_MINB 8 // 64 registers, 32 warps per SM: no spills, constants stay in registers; 10 (48 regs) measured 7 % slower
 #endif
-template <bool COUNT>
+// SELF: test "is this record the lane's own body" (:411).  With eps2 > 0 the test changes nothing:
+// the own body sits at distance 0, so its term is fma(0, m / eps2^1.5, a) = a exactly, as if it had
+// been skipped -- the walk then runs without the compare (and without a stack trip for the own
+// leaf).  eps2 below 1e-60 (0 * inf) and the counting walk keep it.
+template <bool COUNT, bool SELF>
 __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_kernel(const TravArgs a)
 {
     __shared__ uint2 s_stack[TRAV_WARPS][TRAV_STACK]; // {cell id | depth << 27, lanes that must open it}
@@ -451,10 +455,24 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
 #else
         const bool far = thr < r2;
 #endif
-        const bool take = mine & far & (ent != (int)k); // no short circuit
+        const bool take = SELF ? (mine & far & (ent != (int)k)) : (mine & far); // no short circuit
         const double s0 = bh_inv_r3_times_m(r2, c.w);
+#ifdef NB_BH_SELECT_S
         const double s = take ? s0 : 0.0; // selected after the fact: a NaN/inf of a lane that does not take it is dropped
         ax = fma(dx, s, ax); ay = fma(dy, s, ay); az = fma(dz, s, az);
+#else
+        // three predicated DFMAs: the same issue slots as unpredicated ones, and no two FSELs to
+        // zero s first (a NaN/inf of a lane that does not take the candidate never reaches the sums)
+        // (volatile asm: the compiler would otherwise speculate the FMAs and select the sums,
+        // six FSELs; ptxas turns the short branch into predicates)
+        if (take) {
+            asm volatile("fma.rn.f64 %0, %3, %6, %0;\n\t"
+                         "fma.rn.f64 %1, %4, %6, %1;\n\t"
+                         "fma.rn.f64 %2, %5, %6, %2;"
+                         : "+d"(ax), "+d"(ay), "+d"(az)
+                         : "d"(dx), "d"(dy), "d"(dz), "d"(s0));
+        }
+#endif
         if (COUNT) {
             n_inter += take;
             n_visit += ent >= 0 ? take : mine; // the body's own leaf is never visited
@@ -490,7 +508,7 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
             if (COUNT) n_tests += cn;
             continue;
         }
-        // The node's child records are one 512-byte block: the 32 lanes copy 16 bytes each
+        // The node's child records are one 384-byte block: 24 lanes copy 16 bytes each
         // (one coalesced round trip per opened cell) into shared memory, from where all lanes
         // read the records as broadcasts.  How many records count is in the stack word.  Two
         // buffers alternate, so one barrier per cell orders everything: a lane that runs ahead
@@ -499,8 +517,9 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
         const int nc = (int)((top.x >> BH_CODE_NC_SHIFT) & 7u) + 1;
         ChildRec *slot = s_child[warp][flip];
         flip ^= 1;
-        reinterpret_cast<uint4 *>(slot)[lane] =
-            reinterpret_cast<const uint4 *>(cblock + (size_t)nd * 8)[lane];
+        if (lane < (int)BH_BLOCK_WORDS)
+            reinterpret_cast<uint4 *>(slot)[lane] =
+                reinterpret_cast<const uint4 *>(cblock + (size_t)nd * 8)[lane];
         if (sp + nc > TRAV_STACK) { // cannot happen for depth <= BH_MAX_LEVEL; flagged, not silent
             if (lane == 0) a.flags[1] = 1;
             break;
@@ -508,8 +527,10 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
         __syncwarp();
         // Children last to first; a lane notes in `open` (bit c) the candidates it did not take:
         // cells it must descend into (and, once per walk, its own body's leaf).
-        unsigned open = 0;
         if (COUNT) n_tests += (unsigned)nc;
+        // (one jump per cell into eight straight-line copies was measured 3 % slower than this
+        // loop, which the compiler unrolls by four: every copy re-made its constants)
+        unsigned open = 0;
         for (int c = nc - 1; c >= 0; --c) {
             const double4 cc = slot[c].c;
             const double2 be = *reinterpret_cast<const double2 *>(&slot[c].b2); // b2 | ent, code
@@ -594,7 +615,7 @@ static unsigned bh_node_cap(unsigned n) { return (unsigned)bh_node_cap_of(n); }
 size_t bh_bytes(unsigned n)
 {
     const size_t cap = bh_node_cap(n), nn = n ? n : 1;
-    return nn * (2 * 8 + 2 * 4 + 32 + 4) + cap * (32 + 32 + 4 + 4 + 1 + 512 + 4) +
+    return nn * (2 * 8 + 2 * 4 + 32 + 4) + cap * (32 + 32 + 4 + 4 + 1 + 384 + 4) +
            (size_t)256 * bh_sort_blocks(n) * 4 + 4096;
 }
 
@@ -737,8 +758,16 @@ static cudaError_t bh_after_sort(BhTree *t, const BhParams &p, cudaStream_t s, u
     const unsigned max_own = sliced ? (p.own_end > p.own_begin ? min(p.own_end, n) - min(p.own_begin, n) : 0u) : n;
     if (max_own) {
         const unsigned tgrid = (max_own + TRAV_WARPS * 32 - 1) / (TRAV_WARPS * 32);
-        if (p.count_visits) traverse_kernel<true><<<tgrid, TRAV_WARPS * 32, 0, s>>>(ta);
-        else traverse_kernel<false><<<tgrid, TRAV_WARPS * 32, 0, s>>>(ta);
+#ifdef NB_BH_ALWAYS_SELF
+        const bool self = true;
+#else
+        // m / eps2^1.5 must stay finite for the own body's zero term to vanish: any softening a run
+        // would use (the reference's is 0.01) is far above the bound
+        const bool self = !(p.eps2 >= 1e-60);
+#endif
+        if (p.count_visits) traverse_kernel<true, true><<<tgrid, TRAV_WARPS * 32, 0, s>>>(ta);
+        else if (self) traverse_kernel<false, true><<<tgrid, TRAV_WARPS * 32, 0, s>>>(ta);
+        else traverse_kernel<false, false><<<tgrid, TRAV_WARPS * 32, 0, s>>>(ta);
         ++nl;
     }
     BH_TRY(stage_end(t, p, ST_TRAV, s));

@@ -17,14 +17,17 @@ namespace nb {
 
 constexpr int BH_MAX_LEVEL = 21; // 3 x 21 = 63 key bits; deeper cells become buckets
 
-// A child as the traversal sees it (64 bytes, 2 per 128-byte line).
-struct __align__(32) ChildRec {
+// A child as the traversal sees it: 48 bytes, three 16-byte words, so a node's block of eight is
+// 384 bytes = three 128-byte lines (round 1 padded the record to 64 bytes: a quarter of the tree's
+// bytes, written by the build and read by every walk that opens the cell, were padding).
+struct __align__(16) ChildRec {
     double4 c;  // body: x,y,z,m; cell: centre of mass + mass
     double b2;  // cell: acceptance threshold border^2 / THETA^2 + eps2 (tested against dist^2 + eps2); body: -1
     int ent;    // >= 0 body (sorted index), <= -2 cell -(id + 2)
     int code;   // cell: what the walk pushes to open it -- id | (children - 1) << 27 | bucket << 30
-    int pad[4];
 };
+static_assert(sizeof(ChildRec) == 48, "child record: three 16-byte words");
+constexpr unsigned BH_BLOCK_WORDS = 8 * sizeof(ChildRec) / 16; // 16-byte words per node block (24)
 constexpr unsigned BH_CODE_ID = 0x07ffffffu; // 27 bits of node id
 constexpr int BH_CODE_NC_SHIFT = 27;         // 3 bits: non-empty children - 1
 constexpr unsigned BH_CODE_BUCKET = 1u << 30; // a finest-level cell: bodies summed directly
@@ -49,7 +52,7 @@ struct BhTree {
     int *child = nullptr;     // [node][8]: -1 empty, >= 0 body (sorted index), <= -2 node -(c+2)
     unsigned *first = nullptr, *count = nullptr; // the node's bodies: sorted range
     unsigned char *level = nullptr;              // depth (root = 0)
-    // what the traversal reads: per node one 512-byte block of up to 8 child records
+    // what the traversal reads: per node one 384-byte block of up to 8 child records
     // (non-empty children packed to the front, octant order kept), each carrying
     // everything the walk needs about the child -- so opening a cell is ONE round trip
     struct ChildRec *cblock = nullptr; // [node][8]

@@ -127,6 +127,8 @@ struct nb_engine {
     int bh_emulate_runs = 0;
     bool step_ended_in_gather = false;
     cudaEvent_t ev_step0 = nullptr, ev_step1 = nullptr, ev_f0 = nullptr, ev_f1 = nullptr;
+    cudaEvent_t ev_x0 = nullptr; // side stream, just before the position exchange (ev_gather ends it)
+    bool have_x_ev = false;
     bool have_step_ev = false, have_force_ev = false;
     bool time_force = true; // nb_step times only the last evaluation of a multi-step call
     void *q[2] = {nullptr, nullptr};
@@ -222,8 +224,10 @@ int all_gather_bytes(nb_engine *e, void *buf, size_t bytes)
     const char *send = (const char *)buf + (size_t)e->cfg.rank * bytes;
     NB_CUDA(cudaEventRecord(e->ev_compute, e->stream));
     NB_CUDA(cudaStreamWaitEvent(e->comm_stream, e->ev_compute, 0));
+    NB_CUDA(cudaEventRecord(e->ev_x0, e->comm_stream));
     NB_NCCL(g_nccl.AllGather(send, buf, bytes, /*ncclInt8*/ 0, e->comm, e->comm_stream));
     NB_CUDA(cudaEventRecord(e->ev_gather, e->comm_stream));
+    e->have_x_ev = true;
     e->gather_pending = true;
     e->step_ended_in_gather = false; // nb_step sets it again for the gather that ends a step
     e->st.collectives++;
@@ -613,7 +617,7 @@ void nb_free(nb_engine *e)
     if (e->copy_stream) cudaStreamSynchronize(e->copy_stream);
     for (void *b : bufs)
         if (b) cudaFree(b);
-    cudaEvent_t evs[] = {e->ev_step0, e->ev_step1, e->ev_f0, e->ev_f1, e->ev_compute, e->ev_gather,
+    cudaEvent_t evs[] = {e->ev_x0, e->ev_step0, e->ev_step1, e->ev_f0, e->ev_f1, e->ev_compute, e->ev_gather,
                          e->ev_max, e->ev_runs,
                          e->ev_frame_ready[0], e->ev_frame_ready[1], e->ev_frame_done[0],
                          e->ev_frame_done[1]};
@@ -642,6 +646,7 @@ static int init_impl(nb_engine *e, const double *pos, const double *vel)
     NB_CUDA(cudaEventCreate(&e->ev_step1));
     NB_CUDA(cudaEventCreate(&e->ev_f0));
     NB_CUDA(cudaEventCreate(&e->ev_f1));
+    NB_CUDA(cudaEventCreate(&e->ev_x0));
     if (c.world > 1) {
         NB_CUDA(cudaStreamCreateWithFlags(&e->comm_stream, cudaStreamNonBlocking));
         NB_CUDA(cudaEventCreateWithFlags(&e->ev_compute, cudaEventDisableTiming));
@@ -1056,6 +1061,12 @@ int nb_tree_stats(nb_engine *e, nb_tree_info *out)
     out->node_visits = bs.visits;
     out->child_tests = bs.child_tests;
     for (int k = 0; k < 8; ++k) out->stage_ms[k] = k < BH_STAGES ? bs.stage_ms[k] : 0.0;
+    if (e->have_x_ev && e->comm_stream) { // the last position exchange, waiting for the slowest rank included
+        NB_CUDA(cudaStreamSynchronize(e->comm_stream));
+        float ms = 0.f;
+        NB_CUDA(cudaEventElapsedTime(&ms, e->ev_x0, e->ev_gather));
+        out->stage_ms[7] = ms;
+    }
     out->pool_overflow = (int)bs.pool_overflow;
     out->stack_overflow = (int)bs.stack_overflow;
     if (bs.pool_overflow || bs.stack_overflow) {

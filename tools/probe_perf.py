@@ -23,7 +23,7 @@ def run(spec):
     plummer = False
     n = int(parts[1])
     opts = parts[2].split(",") if len(parts) > 2 else []
-    flags, ctas, steps = 0, 0, 3
+    flags, ctas, steps, burst = 0, 0, 3, 0
     for o in opts:
         if o == "scalar":
             flags |= nb.TUNE_SCALAR_FP32
@@ -35,6 +35,8 @@ def run(spec):
             flags |= int(o[8:]) << 8
         elif o.startswith("steps="):
             steps = int(o[6:])
+        elif o.startswith("burst="):
+            burst = int(o[6:])
         elif o == "nouniform":
             flags |= nb.TUNE_NO_UNIFORM
         elif o == "nograph":
@@ -61,6 +63,14 @@ def run(spec):
             st = e.stats()
             times.append(st.last_force_ms)
         st = e.stats()
+        if burst: # one nb_step(burst) call: what a caller that does not read back every step sees
+            per = []
+            for _ in range(5):
+                e.step(burst)
+                per.append(e.stats().last_step_ms / burst * 1e3)
+            print(json.dumps({"spec": spec, "n": n, "us_per_step_in_burst": [round(x, 2) for x in per],
+                              "grid": st.grid, "block": st.block, "variant": st.kernel_variant}), flush=True)
+            return
         best, med = min(times), float(np.median(times))
         out = {"spec": spec, "n": n, "grid": st.grid, "block": st.block,
                "force_ms_min": best, "force_ms_med": med,
