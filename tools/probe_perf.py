@@ -35,6 +35,8 @@ def run(spec):
             flags |= int(o[8:]) << 8
         elif o.startswith("steps="):
             steps = int(o[6:])
+        elif o.startswith("emulate="):  # Barnes-Hut on one GPU: sort as K slices + merge (the multi-rank pipeline)
+            flags |= int(o[8:]) << nb.TUNE_EMULATE_RUNS_SHIFT
         elif o.startswith("burst="):
             burst = int(o[6:])
         elif o == "nouniform":
