@@ -493,9 +493,10 @@ def direct_roofline(nb, prec, uniform_mass, my_rows, n_padded, force_ms_per_step
     else:
         roof["peak_measured_dfma"] = FP64_PEAK_MEASURED_TFLOPS
         roof["frac_of_measured_dfma"] = ach / FP64_PEAK_MEASURED_TFLOPS
-        # 16 FP64-pipe operations + 1 MUFU per interaction at the measured 62.2 DFMA lanes/clk/SM
-        roof["ceiling_of_instruction_mix"] = (SM_COUNT * DFMA_LANES_MEASURED / 16.0 * SM_MAX_MHZ * 1e6
-                                              * FLOP_PER_INTERACTION / 1e12)
+        # 16 (equal masses: 15) FP64-pipe operations + 1 MUFU per interaction at the measured 62.2
+        # DFMA lanes/clk/SM
+        roof["ceiling_of_instruction_mix"] = (SM_COUNT * DFMA_LANES_MEASURED / (15.0 if uniform_mass else 16.0)
+                                              * SM_MAX_MHZ * 1e6 * FLOP_PER_INTERACTION / 1e12)
     roof["frac_of_instruction_mix_ceiling"] = ach / roof["ceiling_of_instruction_mix"]
     if clocks and clocks.get("sm_mhz"):
         roof["frac_at_observed_clock"] = ach / (peak * clocks["sm_mhz"] / SM_MAX_MHZ)
@@ -531,7 +532,8 @@ def direct_record(ctx, what, pm, vel, prec, steps, warmup, tune_flags=0, target_
 
 def kernel_name(nb, prec, uniform_mass, variant=None):
     if prec != nb.PREC_FP32:
-        return "direct_f64_kernel (variant %s): 16 FP64-pipe ops + 1 MUFU per interaction" % variant
+        return ("direct_f64_kernel (variant %s%s): %d FP64-pipe ops + 1 MUFU per interaction"
+                % (variant, ", equal masses: m_j hoisted" if uniform_mass else "", 15 if uniform_mass else 16))
     # nb_direct_f32.cu kVariants: 0..2 pack two j-bodies per register pair (direct_f32_kernel),
     # 3.. pack two i-bodies and take j as a broadcast scalar operand (direct_f32_ip_kernel)
     name = "direct_f32_kernel, j-packed f32x2" if variant is not None and variant < 3 else \

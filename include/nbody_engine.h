@@ -79,7 +79,7 @@ typedef struct nb_config {
 #define NB_TUNE_SCALAR_FP32 1 /* FP32 kernel without packed f32x2 instructions */
 #define NB_TUNE_NO_SPLIT 2    /* one CTA per i-block over all j (no j-range splitting) */
 #define NB_TUNE_NO_OVERLAP 4  /* world > 1: wait for the all-gather before any force work */
-#define NB_TUNE_NO_UNIFORM 16  /* FP32: keep m_j in the inner loop even when all masses are equal */
+#define NB_TUNE_NO_UNIFORM 16  /* direct sum: keep m_j in the inner loop even when all masses are equal */
 #define NB_TUNE_COUNT_VISITS 8 /* Barnes-Hut: count interactions / node visits (nb_tree_stats) */
 #define NB_TUNE_NO_REORDER 32  /* Barnes-Hut: keep the caller's body order on the device */
 #define NB_TUNE_NO_INTERLEAVE 64 /* Barnes-Hut, world > 1: rank slices = contiguous pieces of the Morton curve */
@@ -102,9 +102,9 @@ typedef struct nb_stats {
     size_t n, n_padded, slice_begin, slice_end;
     unsigned long long collectives;       /* all-gathers issued since nb_init (world > 1) */
     unsigned long long split_evaluations; /* force evaluations issued as own-slice + gathered launches */
-    int uniform_mass; /* 1: FP32 direct kernel runs with the mass multiply hoisted (all masses equal) */
+    int uniform_mass; /* 1: the direct kernel runs with the mass multiply hoisted (all masses equal) */
     int kernel_variant; /* direct sum: index of the size class the plan chose (FP32: 0..2 j-packed,
-                         * 3..8 i-packed, nb_direct_f32.cu; FP64: nb_direct_f64.cu); -1 for Barnes-Hut */
+                         * 3..8 i-packed, nb_direct_f32.cu; FP64: 0..2 two, 3..5 four i-bodies per thread, nb_direct_f64.cu); -1 for Barnes-Hut */
 } nb_stats;
 
 /* Fills cfg with the reference's constants: FP64, direct, eps2 = 0.01, G = 1,

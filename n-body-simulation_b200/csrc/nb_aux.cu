@@ -9,19 +9,27 @@
 namespace nb {
 namespace {
 
-// Are all masses equal as floats (and positive)?  cls[0] starts at 1 (mass_class below) and is
-// cleared by any thread that sees a different mass; cls[1] = bits of (float)m_0.  The FP32
-// direct kernel then drops m_j from its inner loop (nb_direct_f32.cu MODE 2).  Runs on the
-// staged host packing, so the host never walks the masses itself.
+// Are all masses equal (as floats for an FP32 engine, as doubles for an FP64 one) and positive?
+// cls[0] starts at 1 (mass_class below) and is cleared by any thread that sees a different
+// mass; cls[1] = bits of (float)m_0, cls[2..3] = bits of m_0.  The direct kernels then drop m_j
+// from their inner loops (nb_direct_f32.cu MODE 2, nb_direct_f64.cu UNI).  Runs on the staged
+// host packing, so the host never walks the masses itself.
+template <bool F64>
 __global__ void mass_class_kernel(const double *__restrict__ pos, unsigned n, unsigned *__restrict__ cls)
 {
-    const float m0 = (float)pos[3];
+    const double d0 = pos[3];
+    const float m0 = (float)d0;
     bool differ = false;
-    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-        differ |= (float)pos[4 * (size_t)i + 3] != m0;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const double m = pos[4 * (size_t)i + 3];
+        differ |= F64 ? (m != d0) : ((float)m != m0);
+    }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         cls[1] = __float_as_uint(m0);
-        differ |= !(m0 > 0.f);
+        cls[2] = (unsigned)__double2loint(d0);
+        cls[3] = (unsigned)__double2hiint(d0);
+        // finite and positive; FP64: G*m and m / eps2^1.5 must stay ordinary numbers
+        differ |= F64 ? !(d0 > 1e-200 && d0 < 1e200) : !(m0 > 0.f);
     }
     if (__any_sync(0xffffffffu, differ) && (threadIdx.x & 31) == 0) cls[0] = 0u;
 }
@@ -65,14 +73,18 @@ __global__ void pack_f32_kernel(const double *__restrict__ pos, const double *__
 
 __global__ void pack_f64_kernel(const double *__restrict__ pos, const double *__restrict__ vel,
                                 unsigned n, unsigned n_pad, double4 *__restrict__ q0,
-                                double4 *__restrict__ q1, double4 *__restrict__ v)
+                                double4 *__restrict__ q1, double4 *__restrict__ v,
+                                const unsigned *__restrict__ cls)
 {
     const unsigned b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= n_pad) return;
     const bool real = b < n;
+    // padding: massless at the origin, or (equal-mass kernel, which ignores m_j) at 1e150, where
+    // r2 = 3e300 is finite and y0^3 = 1.9e-451 underflows to exactly 0
+    const double pad = (cls && cls[0]) ? 1.0e150 : 0.0;
     const double4 p = real ? make_double4(pos[4 * (size_t)b], pos[4 * (size_t)b + 1],
                                           pos[4 * (size_t)b + 2], pos[4 * (size_t)b + 3])
-                           : make_double4(0, 0, 0, 0);
+                           : make_double4(pad, pad, pad, 0);
     q0[b] = p;
     q1[b] = p;
     if (v)
@@ -245,14 +257,16 @@ __global__ void __launch_bounds__(ETB)
 inline unsigned cdiv(unsigned a, unsigned b) { return (a + b - 1) / b; }
 } // namespace
 
-cudaError_t mass_class(const double *pos, unsigned n, unsigned *cls, bool enabled, cudaStream_t s)
+cudaError_t mass_class(const double *pos, unsigned n, unsigned *cls, bool enabled, bool f64,
+                       cudaStream_t s)
 {
-    const unsigned init[2] = {enabled && n ? 1u : 0u, 0u};
+    const unsigned init[4] = {enabled && n ? 1u : 0u, 0u, 0u, 0u};
     cudaError_t e = cudaMemcpyAsync(cls, init, sizeof(init), cudaMemcpyHostToDevice, s); // pageable: staged at once
     if (e != cudaSuccess) return e;
     if (enabled && n) {
         const unsigned g = cdiv(n, 256) < 1184u ? cdiv(n, 256) : 1184u;
-        mass_class_kernel<<<g, 256, 0, s>>>(pos, n, cls);
+        if (f64) mass_class_kernel<true><<<g, 256, 0, s>>>(pos, n, cls);
+        else mass_class_kernel<false><<<g, 256, 0, s>>>(pos, n, cls);
     }
     return cudaGetLastError();
 }
@@ -265,7 +279,7 @@ cudaError_t pack_bodies(int precision, const double *pos, const double *vel, uns
                                                           (float4 *)q1, (float4 *)v, cls);
     else
         pack_f64_kernel<<<cdiv(n_units, 256), 256, 0, s>>>(pos, vel, n, n_units, (double4 *)q0,
-                                                          (double4 *)q1, (double4 *)v);
+                                                          (double4 *)q1, (double4 *)v, cls);
     return cudaGetLastError();
 }
 

@@ -6,13 +6,15 @@ namespace nb {
 
 // host packing (device copies of pos_xyzm[4n], vel_xyz[3n] or nullptr) -> device layout;
 // both position buffers are filled (masses and padding never change afterwards).
-// cls (FP32 layout only, may be nullptr): the two words of mass_class; cls[0] != 0 parks the
-// padding bodies at 1e18 instead of leaving them massless at the origin.
+// cls (may be nullptr): the four words of mass_class; cls[0] != 0 parks the padding bodies at
+// 1e18 (FP32) / 1e150 (FP64) instead of leaving them massless at the origin.
 cudaError_t pack_bodies(int precision, const double *pos, const double *vel, unsigned n,
                         unsigned n_units, void *q0, void *q1, void *v, const unsigned *cls, cudaStream_t s);
-// cls[0] = 1 iff `enabled` and all n masses of the staged host packing are equal as floats and
-// positive, cls[1] = bits of (float)m_0.  Device-side: the host never scans the masses.
-cudaError_t mass_class(const double *pos, unsigned n, unsigned *cls, bool enabled, cudaStream_t s);
+// cls[0] = 1 iff `enabled` and all n masses of the staged host packing are equal (as floats, or
+// as doubles with f64) and positive, cls[1] = bits of (float)m_0, cls[2..3] = bits of m_0.
+// Device-side: the host never scans the masses.
+cudaError_t mass_class(const double *pos, unsigned n, unsigned *cls, bool enabled, bool f64,
+                       cudaStream_t s);
 // device layout -> host packing; planes = 4 (pos+mass) or 3 (vel / acc)
 // scatter (optional): body b of the device order goes to row scatter[b] of `out`
 cudaError_t unpack_bodies(int precision, const void *src, unsigned n, int planes, double *out,

@@ -15,7 +15,13 @@
 //   * accumulation is plain FP64 in j order inside a CTA's j-range; partial
 //     ranges are added in fixed slot order.
 // Per interaction: 3 DADD + 3 DFMA (r2) + 7 + 3 DFMA = 16 FP64-pipe operations
-// + 1 MUFU.
+// + 1 MUFU.  Equal masses (UNI, detected at upload like in the FP32 engine): m_j leaves the loop
+// (r2^-3/2 alone is 6 operations: 15 per interaction) and the epilogue's G carries G*m; padding
+// bodies, which cannot be massless then, are parked at 1e150 where y0^3 underflows to exactly 0.
+// IPT i-bodies per thread (2 or 4): every j-body read from shared memory (two LDS.128, or
+// LDS.128 + LDS.64 without the mass) serves IPT interactions -- an FP64 instruction occupies the
+// dispatch port for two cycles and everything else for one, so the loads and the
+// loop counter are not free.
 #include "nb_direct.cuh"
 
 namespace nb {
@@ -26,6 +32,18 @@ constexpr int STAGES64 = 4;
 __device__ __forceinline__ void named_sync64(int id, int nthreads)
 {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// (r2)^(-3/2), six operations
+__device__ __forceinline__ double inv_r3(double r2)
+{
+    const double y0 = rsqrt_approx_f64(r2);
+    const double y02 = y0 * y0;
+    const double e = fma(-r2, y02, 1.0);
+    const double pe = fma(1.875, e, 1.5);
+    const double q = e * pe;
+    const double u = y02 * y0;
+    return fma(u, q, u);
 }
 
 // m * (r2)^(-3/2)
@@ -52,12 +70,14 @@ __device__ __forceinline__ double drift64(double x, double v, double dt)
     return __dadd_rn(x, __dmul_rn(v, dt));
 }
 
-template <int NW, int TB, int MINB>
+template <int NW, int TB, int MINB, bool UNI, int IPT>
 __global__ void __launch_bounds__(NW * 32, MINB)
     direct_f64_kernel(const StepParams p)
 {
-    constexpr int TPB = NW * 32;  // compute threads
-    constexpr int BPB = TPB * 2;  // bodies per i-block
+    static_assert(IPT == 2 || IPT == 4, "i-bodies per thread");
+    constexpr int TPB = NW * 32;    // compute threads
+    constexpr int BPB = TPB * IPT;  // bodies per i-block
+    constexpr int HALF = IPT / 2;   // double2 words per thread and component
     __shared__ __align__(128) double4 tiles[STAGES64][TB];
     __shared__ __align__(8) uint64_t full_bar[STAGES64];
     __shared__ __align__(8) uint64_t empty_bar[STAGES64];
@@ -108,17 +128,19 @@ __global__ void __launch_bounds__(NW * 32, MINB)
         const unsigned ib = (unsigned)(w / n_jtiles);
         const unsigned t0 = (unsigned)(w - (unsigned long long)ib * n_jtiles);
         const unsigned cnt = (unsigned)min((unsigned long long)(n_jtiles - t0), w1 - w);
-        unsigned bi[2];
-        bool valid[2];
-        double xi[2], yi[2], zi[2];
+        unsigned bi[IPT];
+        bool valid[IPT];
+        double xi[IPT], yi[IPT], zi[IPT];
 #pragma unroll
-        for (int r = 0; r < 2; ++r) {
+        for (int r = 0; r < IPT; ++r) {
             bi[r] = p.i_begin + ib * BPB + r * TPB + tidc;
             valid[r] = bi[r] < p.i_end;
             const double4 b = q[valid[r] ? bi[r] : p.i_begin];
             xi[r] = b.x; yi[r] = b.y; zi[r] = b.z;
         }
-        double ax[2] = {0, 0}, ay[2] = {0, 0}, az[2] = {0, 0};
+        double ax[IPT], ay[IPT], az[IPT];
+#pragma unroll
+        for (int r = 0; r < IPT; ++r) ax[r] = ay[r] = az[r] = 0.0;
 
         for (unsigned k = 0; k < cnt; ++k) {
             const unsigned first = global_tile(t0 + k) * TB;
@@ -129,16 +151,22 @@ __global__ void __launch_bounds__(NW * 32, MINB)
             const double4 *__restrict__ tile = &tiles[stage][0];
 #pragma unroll 4
             for (int j = 0; j < nb; ++j) {
-                const double4 b = tile[j];
+                double4 b;
+                if (UNI) { // x,y | z: the mass is not read
+                    const double2 xy = *reinterpret_cast<const double2 *>(&tile[j]);
+                    b = make_double4(xy.x, xy.y, tile[j].z, 0.0);
+                } else {
+                    b = tile[j];
+                }
 #pragma unroll
-                for (int r = 0; r < 2; ++r) {
+                for (int r = 0; r < IPT; ++r) {
                     const double dx = b.x - xi[r];
                     const double dy = b.y - yi[r];
                     const double dz = b.z - zi[r];
                     double r2 = fma(dx, dx, p.eps2);
                     r2 = fma(dy, dy, r2);
                     r2 = fma(dz, dz, r2);
-                    const double s = inv_r3_times_m(r2, b.w);
+                    const double s = UNI ? inv_r3(r2) : inv_r3_times_m(r2, b.w);
                     ax[r] = fma(dx, s, ax[r]);
                     ay[r] = fma(dy, s, ay[r]);
                     az[r] = fma(dz, s, az[r]);
@@ -157,12 +185,16 @@ __global__ void __launch_bounds__(NW * 32, MINB)
             const unsigned c_last = p.ws.owner(x0 + n_jtiles - 1);
             const unsigned nslots = c_last - c_first + 1;
             const unsigned slot = blockIdx.x - c_first;
+            constexpr int SLOT = TPB * 3 * HALF; // double2 words per slot
             double2 *ws = reinterpret_cast<double2 *>(p.workspace) +
-                          ((size_t)ib * p.max_slots) * (size_t)(TPB * 3);
-            double2 *mine = ws + (size_t)slot * (TPB * 3);
-            mine[0 * TPB + tidc] = make_double2(ax[0], ax[1]);
-            mine[1 * TPB + tidc] = make_double2(ay[0], ay[1]);
-            mine[2 * TPB + tidc] = make_double2(az[0], az[1]);
+                          ((size_t)ib * p.max_slots) * (size_t)SLOT;
+            double2 *mine = ws + (size_t)slot * SLOT;
+#pragma unroll
+            for (int h = 0; h < HALF; ++h) {
+                mine[(0 * HALF + h) * TPB + tidc] = make_double2(ax[2 * h], ax[2 * h + 1]);
+                mine[(1 * HALF + h) * TPB + tidc] = make_double2(ay[2 * h], ay[2 * h + 1]);
+                mine[(2 * HALF + h) * TPB + tidc] = make_double2(az[2 * h], az[2 * h + 1]);
+            }
             __threadfence();
             named_sync64(1, TPB);
             if (tidc == 0) {
@@ -175,13 +207,17 @@ __global__ void __launch_bounds__(NW * 32, MINB)
             do_epilogue = (s_last != 0);
             if (do_epilogue) {
                 __threadfence();
-                ax[0] = ax[1] = ay[0] = ay[1] = az[0] = az[1] = 0.0;
+#pragma unroll
+                for (int r = 0; r < IPT; ++r) ax[r] = ay[r] = az[r] = 0.0;
                 for (unsigned s = 0; s < nslots; ++s) {
-                    const double2 *src = ws + (size_t)s * (TPB * 3);
-                    double2 v;
-                    v = __ldcg(&src[0 * TPB + tidc]); ax[0] += v.x; ax[1] += v.y;
-                    v = __ldcg(&src[1 * TPB + tidc]); ay[0] += v.x; ay[1] += v.y;
-                    v = __ldcg(&src[2 * TPB + tidc]); az[0] += v.x; az[1] += v.y;
+                    const double2 *src = ws + (size_t)s * SLOT;
+#pragma unroll
+                    for (int h = 0; h < HALF; ++h) {
+                        double2 v;
+                        v = __ldcg(&src[(0 * HALF + h) * TPB + tidc]); ax[2 * h] += v.x; ax[2 * h + 1] += v.y;
+                        v = __ldcg(&src[(1 * HALF + h) * TPB + tidc]); ay[2 * h] += v.x; ay[2 * h + 1] += v.y;
+                        v = __ldcg(&src[(2 * HALF + h) * TPB + tidc]); az[2 * h] += v.x; az[2 * h + 1] += v.y;
+                    }
                 }
             }
             named_sync64(1, TPB);
@@ -189,23 +225,26 @@ __global__ void __launch_bounds__(NW * 32, MINB)
 
         // multi-rank: sums parked between the own-slice and the gathered j-ranges
         if (do_epilogue && (p.flags & (NB_F_PARTIAL_IN | NB_F_PARTIAL_OUT))) {
-            double2 *park = reinterpret_cast<double2 *>(p.partial) + (size_t)ib * (TPB * 3);
-            if (p.flags & NB_F_PARTIAL_IN) {
-                double2 v;
-                v = park[0 * TPB + tidc]; ax[0] += v.x; ax[1] += v.y;
-                v = park[1 * TPB + tidc]; ay[0] += v.x; ay[1] += v.y;
-                v = park[2 * TPB + tidc]; az[0] += v.x; az[1] += v.y;
-            } else {
-                park[0 * TPB + tidc] = make_double2(ax[0], ax[1]);
-                park[1 * TPB + tidc] = make_double2(ay[0], ay[1]);
-                park[2 * TPB + tidc] = make_double2(az[0], az[1]);
-                do_epilogue = false;
+            double2 *park = reinterpret_cast<double2 *>(p.partial) + (size_t)ib * (TPB * 3 * HALF);
+#pragma unroll
+            for (int h = 0; h < HALF; ++h) {
+                if (p.flags & NB_F_PARTIAL_IN) {
+                    double2 v;
+                    v = park[(0 * HALF + h) * TPB + tidc]; ax[2 * h] += v.x; ax[2 * h + 1] += v.y;
+                    v = park[(1 * HALF + h) * TPB + tidc]; ay[2 * h] += v.x; ay[2 * h + 1] += v.y;
+                    v = park[(2 * HALF + h) * TPB + tidc]; az[2 * h] += v.x; az[2 * h + 1] += v.y;
+                } else {
+                    park[(0 * HALF + h) * TPB + tidc] = make_double2(ax[2 * h], ax[2 * h + 1]);
+                    park[(1 * HALF + h) * TPB + tidc] = make_double2(ay[2 * h], ay[2 * h + 1]);
+                    park[(2 * HALF + h) * TPB + tidc] = make_double2(az[2 * h], az[2 * h + 1]);
+                }
             }
+            if (!(p.flags & NB_F_PARTIAL_IN)) do_epilogue = false;
         }
 
         if (do_epilogue) {
 #pragma unroll
-            for (int r = 0; r < 2; ++r) {
+            for (int r = 0; r < IPT; ++r) {
                 if (!valid[r]) continue;
                 const unsigned b = bi[r];
                 const double a3[3] = {p.G * ax[r], p.G * ay[r], p.G * az[r]};
@@ -239,22 +278,43 @@ __global__ void __launch_bounds__(NW * 32, MINB)
 }
 
 struct VariantF64 {
-    int nw, tb, minb;
+    int nw, tb, minb, ipt;
 };
-constexpr int kNumVariants64 = 3;
+#ifndef NB_F64_LARGE_VARIANT
+#define NB_F64_LARGE_VARIANT 4
+#endif
+constexpr int kNumVariants64 = 8;
 constexpr VariantF64 kVariants64[kNumVariants64] = {
-    {8, 128, 2}, // large : i-block 512 bodies
-    {4, 128, 4}, // medium: i-block 256 bodies
-    {1, 32, 8},  // small : i-block 64 bodies
+    {8, 128, 2, 2}, // 0 round 1's large class: i-block 512 bodies
+    {4, 128, 4, 2}, // 1 medium: i-block 256 bodies
+    {1, 32, 8, 2},  // 2 small : i-block 64 bodies
+    {8, 128, 2, 4}, // 3 large, 4 i-bodies per thread: i-block 1024 bodies, <= 128 registers
+    {8, 128, 1, 4}, // 4 the same with one CTA per SM
+    {4, 128, 4, 4}, // 5 medium, 4 i-bodies per thread
+    {16, 128, 1, 4}, // 6 one CTA of 16 warps per SM
+    {4, 128, 2, 4}, // 7 medium, two CTAs of 4 warps, registers uncapped
 };
 
-template <int NW, int TB, int MINB>
+// X(index, NW, TB, MINB, IPT)
+#define NB_F64_VARIANTS(X) \
+    X(0, 8, 128, 2, 2)     \
+    X(1, 4, 128, 4, 2)     \
+    X(2, 1, 32, 8, 2)      \
+    X(3, 8, 128, 2, 4)     \
+    X(4, 8, 128, 1, 4)     \
+    X(5, 4, 128, 4, 4)     \
+    X(6, 16, 128, 1, 4)    \
+    X(7, 4, 128, 2, 4)
+
+template <int NW, int TB, int MINB, int IPT>
 int occupancy64()
 {
-    int n = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, direct_f64_kernel<NW, TB, MINB>,
+    int n = 0, m = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, direct_f64_kernel<NW, TB, MINB, false, IPT>,
                                                   NW * 32, 0);
-    return n;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&m, direct_f64_kernel<NW, TB, MINB, true, IPT>,
+                                                  NW * 32, 0);
+    return n < m ? n : m;
 }
 } // namespace
 
@@ -262,25 +322,30 @@ cudaError_t plan_direct_f64(DirectPlan *plan, const SliceGeom &sg, int sm_count,
                             int tune_flags)
 {
     const unsigned slice_units = sg.slice_units, n_units = sg.n_units;
-    // by work (i x j); measured: large wins at 50k^2, medium at 20k^2, small at 8k^2
+    // by work (i x j); measured (round 2, profiles/r2_direct_f64_variants_*.jsonl): the large
+    // class (one CTA of 8 warps per SM, 4 i-bodies per thread, 174 registers) wins from 20k^2 up
+    // (20k: 0.404 vs 0.412 ms medium; 30k: 0.859 vs 0.901; 100k: 9.24 vs 9.56 for round 1's
+    // large class), small at 10k^2 and below
     const double work = (double)slice_units * (double)n_units;
-    int v = work >= 1.6e9 ? 0 : (work >= 1.44e8 ? 1 : 2);
+    int v = work >= 3.5e8 ? NB_F64_LARGE_VARIANT : (work >= 1.44e8 ? 1 : 2);
     const int forced = (tune_flags >> 8) & 0xf;
     if (forced >= 1 && forced <= kNumVariants64) v = forced - 1;
     const VariantF64 &k = kVariants64[v];
     plan->precision = 0;
     plan->variant = v;
-    plan->units_per_iblock = (unsigned)k.nw * 64u;
+    plan->units_per_iblock = (unsigned)(k.nw * 32 * k.ipt);
     plan->units_per_tile = (unsigned)k.tb;
     plan->n_iblocks = (slice_units + plan->units_per_iblock - 1) / plan->units_per_iblock;
     plan->n_jtiles = (n_units + plan->units_per_tile - 1) / plan->units_per_tile;
     plan->block = (unsigned)k.nw * 32u;
-    plan->slot_doubles = (size_t)k.nw * 32 * 6;
+    plan->slot_doubles = (size_t)k.nw * 32 * 3 * k.ipt;
     int occ = 0;
     switch (v) {
-    case 0: occ = occupancy64<8, 128, 2>(); break;
-    case 1: occ = occupancy64<4, 128, 4>(); break;
-    default: occ = occupancy64<1, 32, 8>(); break;
+#define X(I, NW, TB, MINB, IPT) \
+    case I: occ = occupancy64<NW, TB, MINB, IPT>(); break;
+        NB_F64_VARIANTS(X)
+#undef X
+    default: break;
     }
     cudaError_t err = cudaGetLastError();
     if (err != cudaSuccess) return err;
@@ -297,10 +362,16 @@ cudaError_t launch_direct_f64(const DirectPlan &plan, int geom, StepParams p, in
 {
     (void)tune_flags;
     apply_geom(plan, geom, &p);
+    const bool uni = p.uniform_mass != 0;
     switch (plan.variant) {
-    case 0: direct_f64_kernel<8, 128, 2><<<p.ws.n_ctas, plan.block, 0, stream>>>(p); break;
-    case 1: direct_f64_kernel<4, 128, 4><<<p.ws.n_ctas, plan.block, 0, stream>>>(p); break;
-    default: direct_f64_kernel<1, 32, 8><<<p.ws.n_ctas, plan.block, 0, stream>>>(p); break;
+#define X(I, NW, TB, MINB, IPT)                                                                      \
+    case I:                                                                                          \
+        if (uni) direct_f64_kernel<NW, TB, MINB, true, IPT><<<p.ws.n_ctas, plan.block, 0, stream>>>(p); \
+        else direct_f64_kernel<NW, TB, MINB, false, IPT><<<p.ws.n_ctas, plan.block, 0, stream>>>(p);  \
+        break;
+        NB_F64_VARIANTS(X)
+#undef X
+    default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();
 }

@@ -140,7 +140,7 @@ struct nb_engine {
     // host I/O slices (nb_upload_slice / nb_gather_slice): rank r moves rows [r*io_per, (r+1)*io_per)
     // of the caller's order over PCIe, the rest travels between the GPUs (all-gather of the staging rows)
     size_t io_per = 0;
-    unsigned *mass_cls = nullptr; // device: [0] all masses equal (FP32 direct), [1] bits of (float)m_0
+    unsigned *mass_cls = nullptr; // device: [0] all masses equal (direct sum), [1] bits of (float)m_0, [2..3] of m_0
     double *energy_part = nullptr;
     // frame pipeline (nb_frame_begin / nb_frame_wait), created on first use
     cudaStream_t copy_stream = nullptr;
@@ -170,7 +170,7 @@ struct nb_engine {
     bool bh_graphs_off = false;
     bool bh = false;
     bool count_visits = false;
-    bool uniform = false;   // FP32 direct: all masses equal (as floats) -> mass-free inner loop
+    bool uniform = false;   // direct sum: all masses equal -> mass-free inner loop
     double uniform_m = 0.0;
     State state = SYNCED_NOACC;
     void *comm = nullptr;
@@ -499,9 +499,10 @@ int upload(nb_engine *e, const double *pos, const double *vel, bool sliced)
     // loop and the epilogue multiplies by G*m.  Padding then has to be inert without a zero
     // mass: it is parked so far away that r^-3 underflows to exactly 0.  The masses are
     // classified on the device (mass_class), from the staged rows; the host reads two words.
-    const bool classify = e->cfg.precision == NB_PREC_FP32 && !e->bh && n > 0 &&
-                          !(e->cfg.tune_flags & (NB_TUNE_SCALAR_FP32 | NB_TUNE_NO_UNIFORM));
-    NB_CUDA(mass_class(e->stage_pos, (unsigned)n, e->mass_cls, classify, e->stream));
+    const bool f64 = e->cfg.precision != NB_PREC_FP32;
+    const bool classify = !e->bh && n > 0 && !(e->cfg.tune_flags & NB_TUNE_NO_UNIFORM) &&
+                          (f64 || !(e->cfg.tune_flags & NB_TUNE_SCALAR_FP32));
+    NB_CUDA(mass_class(e->stage_pos, (unsigned)n, e->mass_cls, classify, f64, e->stream));
     if (classify) e->st.kernel_launches++;
     // overflow flags of the tree stay set between evaluations (a truncated tree must be caught
     // at the next gather) but not across a new state
@@ -529,13 +530,15 @@ int upload(nb_engine *e, const double *pos, const double *vel, bool sliced)
     NB_CUDA(pack_bodies(e->cfg.precision, e->stage_pos, vel ? e->stage_vel : nullptr, (unsigned)n,
                         e->n_units, e->q[0], e->q[1], e->vel, e->mass_cls, e->stream));
     e->st.kernel_launches++;
-    unsigned cls[2] = {0u, 0u};
+    unsigned cls[4] = {0u, 0u, 0u, 0u};
     NB_CUDA(cudaMemcpyAsync(cls, e->mass_cls, sizeof(cls), cudaMemcpyDeviceToHost, e->stream));
     NB_CUDA(cudaStreamSynchronize(e->stream)); // the caller's arrays are free again; cls is in
     float m0;
+    double d0;
     memcpy(&m0, &cls[1], sizeof(m0));
+    memcpy(&d0, &cls[2], sizeof(d0));
     e->uniform = cls[0] != 0u;
-    e->uniform_m = (double)m0;
+    e->uniform_m = f64 ? d0 : (double)m0;
     e->cur = 0;
     e->state = SYNCED_NOACC;
     e->vel_complete = true;
@@ -727,7 +730,7 @@ static int init_impl(nb_engine *e, const double *pos, const double *vel)
     const size_t stage_rows = e->io_per * (size_t)c.world + 1; // whole io slices of every rank
     NB_CUDA(cudaMalloc(&e->stage_pos, stage_rows * 4 * sizeof(double)));
     NB_CUDA(cudaMalloc(&e->stage_vel, stage_rows * 3 * sizeof(double)));
-    NB_CUDA(cudaMalloc(&e->mass_cls, 2 * sizeof(unsigned)));
+    NB_CUDA(cudaMalloc(&e->mass_cls, 4 * sizeof(unsigned)));
     NB_CUDA(cudaMalloc(&e->energy_part, (size_t)(energy_blocks((unsigned)e->n) + 1) * 2 * sizeof(double)));
 
     if (c.world > 1) {

@@ -273,6 +273,39 @@ def test_fp32_ipacked_size_classes(nb, oracle_lib, variant, masses, n):
     assert np.array_equal(p[:, 3], pm[:, 3])
 
 
+@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7, 8])
+@pytest.mark.parametrize("masses", ["equal", "spread"])
+@pytest.mark.parametrize("n", [3, 1000, 2500, 10_000])
+def test_fp64_size_classes_and_equal_masses(nb, oracle_lib, variant, masses, n):
+    """Every FP64 direct kernel (2 and 4 i-bodies per thread; the equal-mass form that drops m_j
+    from the loop and parks the padding at 1e150, and the general form), forced through
+    tune_flags: accelerations against the oracle at 1e-12, 10 leapfrog steps against the reference's
+    propagation at 1e-12, masses returned untouched."""
+    import oracle as O
+    g = golden("10k_bodies_g1")
+    pm, vel = g["pos_xyzm"][:n].copy(), g["vel"][:n].copy()
+    if masses == "spread":
+        pm[:, 3] = np.random.default_rng(n).uniform(0.1, 0.3, n)
+    with nb.Engine(pm, vel, precision=nb.PREC_FP64, tune_flags=variant << 8) as e:
+        st = e.stats()
+        assert st.kernel_variant == variant - 1
+        acc = e.accelerations()
+        assert e.stats().uniform_mass == (1 if masses == "equal" else 0)
+        e.step(10)
+        p, v = e.gather()
+    ref = O.acceleration(oracle_lib, pm, "orc_acceleration_mt", 8)
+    assert rel_err(acc, ref).max() <= 1e-12
+    if n <= 2500:
+        rp, rv = O.propagate(oracle_lib, pm, vel, 10, 0.01, threads=8)
+        assert rel_err(p[:, :3], rp[:, :3]).max() <= 1e-12
+        assert rel_err(v, rv).max() <= 1e-12
+    assert np.array_equal(p[:, 3], pm[:, 3])
+    # the equal-mass form against the general one on the same input
+    with nb.Engine(pm, vel, precision=nb.PREC_FP64, tune_flags=(variant << 8) | nb.TUNE_NO_UNIFORM) as e:
+        assert e.stats().uniform_mass == 0
+        assert rel_err(e.accelerations(), acc).max() <= 1e-13
+
+
 # -------------------------------------------- size-independent properties ---
 @pytest.mark.parametrize("prec,n,masses", [("fp32", 200_000, "spread"), ("fp64", 60_000, "spread"),
                                            ("fp32", 1_000_000, "equal"),    # BASELINE config 3 (bench)
@@ -420,4 +453,11 @@ def test_equal_mass_detection_runs_on_the_device(nb):
         assert e.stats().uniform_mass == 0
         assert rel_err(e.accelerations(), a_uni).max() <= 2e-6
     with nb.Engine(pm, vel, precision=nb.PREC_FP64) as e:
+        assert e.stats().uniform_mass == 1
+        a64 = e.accelerations()
+        pm2[n - 1, 3] = 0.25 * (1 + 2.0 ** -40)   # equal as floats, not as doubles
+        e.upload(pm2, vel)
         assert e.stats().uniform_mass == 0
+        assert rel_err(e.accelerations(), a64).max() <= 1e-11
+    with nb.Engine(pm, vel, precision=nb.PREC_FP64, algorithm=nb.ALGO_BARNES_HUT) as e:
+        assert e.stats().uniform_mass == 0            # the tree needs the masses: never hoisted

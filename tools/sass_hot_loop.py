@@ -4,7 +4,10 @@ the backward-branch loop holding the most instructions matching PATTERN (default
 FP32), with a per-mnemonic count.  Usage: sass_hot_loop.py file.sass [regex]"""
 import collections
 import re
+import signal
 import sys
+
+signal.signal(signal.SIGPIPE, signal.SIG_DFL)
 
 
 def main():
