@@ -157,6 +157,9 @@ struct nb_engine {
     unsigned *user_of = nullptr;
     double *order_tmp = nullptr; // 4n doubles of scratch for the reordering
     unsigned *morton_tmp = nullptr, *chunk_base = nullptr; // world > 1: dealing the curve out to the ranks
+    // NB_DEBUG_OWN_SLICE="W:r" on a one-rank Barnes-Hut engine: lay the state out as W ranks would
+    // and walk only rank r's bodies -- what one rank of a W-GPU run does, measured on one GPU
+    unsigned dbg_world = 0, dbg_rank = 0, dbg_len = 0;
     // A Barnes-Hut evaluation is ~75 short launches with fixed arguments per (ping-pong side,
     // epilogue flags): captured once as a CUDA graph, replayed afterwards.
     struct BhGraph {
@@ -303,6 +306,10 @@ int launch_force(nb_engine *e, unsigned flags)
         bp.n = (unsigned)e->n;
         bp.own_begin = e->i_begin;
         bp.own_end = e->i_end;
+        if (e->dbg_world) {
+            bp.own_begin = e->dbg_rank * e->dbg_len;
+            bp.own_end = std::min<unsigned>((e->dbg_rank + 1) * e->dbg_len, (unsigned)e->n);
+        }
         bp.flags = flags;
         bp.dt = p.dt; bp.eps2 = p.eps2; bp.G = p.G; bp.theta = e->cfg.theta;
         bp.count_visits = e->count_visits ? 1 : 0;
@@ -420,7 +427,9 @@ constexpr unsigned kDealPieces = 32; // pieces per rank (tune_flags bits 16..23:
 
 int deal_curve(nb_engine *e)
 {
-    const unsigned n = (unsigned)e->n, world = (unsigned)e->cfg.world, len = e->slice_units;
+    const unsigned n = (unsigned)e->n;
+    const unsigned world = e->dbg_world ? e->dbg_world : (unsigned)e->cfg.world;
+    const unsigned len = e->dbg_world ? e->dbg_len : e->slice_units;
     const unsigned full = n / kDealChunk, rag = n % kDealChunk;
     std::vector<unsigned> base(full + 1, 0u), fill(world, 0u), cap(world, 0u);
     for (unsigned r = 0; r < world; ++r) {
@@ -718,7 +727,15 @@ static int init_impl(nb_engine *e, const double *pos, const double *vel)
     if (e->bh && e->n > 1 && !(c.tune_flags & NB_TUNE_NO_REORDER)) {
         NB_CUDA(cudaMalloc(&e->user_of, e->n * sizeof(unsigned)));
         NB_CUDA(cudaMalloc(&e->order_tmp, e->n * 4 * sizeof(double)));
-        if (c.world > 1 && !(c.tune_flags & NB_TUNE_NO_INTERLEAVE)) {
+        if (const char *dbg = getenv("NB_DEBUG_OWN_SLICE")) {
+            unsigned w = 0, r = 0;
+            if (c.world == 1 && sscanf(dbg, "%u:%u", &w, &r) == 2 && w > 1 && r < w) {
+                e->dbg_world = w;
+                e->dbg_rank = r;
+                e->dbg_len = (unsigned)(((e->n + w - 1) / w + kSliceAlignF64 - 1) / kSliceAlignF64 * kSliceAlignF64);
+            }
+        }
+        if ((c.world > 1 || e->dbg_world) && !(c.tune_flags & NB_TUNE_NO_INTERLEAVE)) {
             NB_CUDA(cudaMalloc(&e->morton_tmp, e->n * sizeof(unsigned)));
             NB_CUDA(cudaMalloc(&e->chunk_base, (e->n / kDealChunk + 1) * sizeof(unsigned)));
         }

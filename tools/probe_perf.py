@@ -37,6 +37,8 @@ def run(spec):
             steps = int(o[6:])
         elif o.startswith("emulate="):  # Barnes-Hut on one GPU: sort as K slices + merge (the multi-rank pipeline)
             flags |= int(o[8:]) << nb.TUNE_EMULATE_RUNS_SHIFT
+        elif o.startswith("pieces="):  # Barnes-Hut, world > 1: 2^K curve pieces per rank
+            flags |= (int(o[7:]) + 1) << 16
         elif o.startswith("burst="):
             burst = int(o[6:])
         elif o == "nouniform":
