@@ -3,6 +3,7 @@
 // THETA traversal with the leapfrog epilogue fused in.  See nb_bh.cuh for the
 // correspondence with the reference (serial/barnes-hut.c, cuda/barnes-hut.cu).
 #include "nb_bh.cuh"
+#include <stdlib.h>
 #include "nb_common.cuh"
 
 namespace nb {
@@ -409,7 +410,10 @@ __device__ __forceinline__ double bh_inv_r3_times_m(double r2, double m)
 // the own body sits at distance 0, so its term is fma(0, m / eps2^1.5, a) = a exactly, as if it had
 // been skipped -- the walk then runs without the compare (and without a stack trip for the own
 // leaf).  eps2 below 1e-60 (0 * inf) and the counting walk keep it.
-template <bool COUNT, bool SELF>
+// PREFETCH: when a cell is pushed, three lanes ask L2 for the three lines of its child block.  Pays
+// when the tree is far larger than L2 or a rank walks scattered pieces of it (misses stall a walk
+// that has 8 warps per sub-partition to hide them); costs 3 issue slots per push otherwise.
+template <bool COUNT, bool SELF, bool PREFETCH>
 __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_kernel(const TravArgs a)
 {
     __shared__ uint2 s_stack[TRAV_WARPS][TRAV_STACK]; // {cell id | depth << 27, lanes that must open it}
@@ -421,16 +425,29 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
     const ChildRec *__restrict__ cblock = a.cblock;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const unsigned n_own = a.own ? a.flags[2] : a.n_own_static;
-    const unsigned j = (blockIdx.x * TRAV_WARPS + warp) * 32 + lane;
+    const double eps2 = a.p.eps2;
+    uint2 *stk = s_stack[warp];
+    int flip = 0;
+    // One CTA per 128 bodies.  NB_BH_TRAV_DYNAMIC (measured, not shipped) makes the grid resident
+    // and lets every warp fetch its next 32 bodies from a counter, against the idea that CTAs wait
+    // for their slowest warp and the grid drains for a whole walk at the end: 1M Plummer 4.84 ->
+    // 5.05 ms, 16M 82.0 -> 83.4 ms -- the hardware's block scheduler already does it better.
+    for (;;) {
+    unsigned wi = 0;
+#ifndef NB_BH_TRAV_DYNAMIC
+    wi = blockIdx.x * TRAV_WARPS + warp;
+#else
+    if (lane == 0) wi = atomicAdd(&a.flags[4], 1u);
+    wi = __shfl_sync(0xffffffffu, wi, 0);
+#endif
+    if ((unsigned long long)wi * 32ull >= n_own) break;
+    const unsigned j = wi * 32 + lane;
     const bool valid = j < n_own;
     const unsigned k = valid ? (a.own ? a.own[j] : j) : 0u;
     const double4 me = spos[k];
-    const double eps2 = a.p.eps2;
     double ax = 0, ay = 0, az = 0;
     unsigned n_inter = 0, n_visit = 0;
     unsigned n_tests = 0; // records this WARP tested (17 FP64 warp instructions each), same in every lane
-    uint2 *stk = s_stack[warp];
-    int flip = 0;
     int sp = 0;
     const unsigned all = __ballot_sync(0xffffffffu, valid);
 
@@ -546,6 +563,10 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
             todo &= ~(1u << c);
             const int2 ec = *reinterpret_cast<const int2 *>(&slot[c].ent); // ent, code
             if (ec.x >= 0) continue; // a lane's own body
+            if (PREFETCH && lane < 3) {
+                const char *blk = reinterpret_cast<const char *>(cblock + (size_t)((unsigned)ec.y & BH_CODE_ID) * 8);
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(blk + lane * 128));
+            }
             stk[sp++] = make_uint2((unsigned)ec.y, __ballot_sync(0xffffffffu, (open >> c) & 1u));
         }
     }
@@ -563,8 +584,8 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
             atomicAdd(&a.counters[2], (unsigned long long)n_tests);
         }
     }
-    if (!valid) return;
-
+    __syncwarp(); // every lane is done with the stack and the child buffers of this walk
+    if (valid) {
     // ---- epilogue: the direct-sum kernel's (nb_direct_f64.cu): kick2 / kick1 / drift
     const unsigned idx = a.perm[k];
     const BhParams &p = a.p;
@@ -588,6 +609,11 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
             qn[0] = x3[0]; qn[1] = x3[1]; qn[2] = x3[2]; // mass was placed at upload
         }
     }
+    } // valid
+#ifndef NB_BH_TRAV_DYNAMIC
+    break;
+#endif
+    } // next 32 bodies
 }
 
 __global__ void reset_kernel(unsigned *level_count, unsigned *flags, double *bbox, unsigned *first,
@@ -601,6 +627,7 @@ __global__ void reset_kernel(unsigned *level_count, unsigned *flags, double *bbo
         count[0] = n;
         level[0] = 0;
         flags[2] = 0;
+        flags[4] = 0; // the walk's work counter (traverse_kernel)
         if (reset_counters) counters[0] = counters[1] = counters[2] = 0;
     }
 }
@@ -650,8 +677,8 @@ cudaError_t bh_alloc(BhTree *t, unsigned n, unsigned n_keys, unsigned parts)
     BH_TRY(cudaMalloc(&t->cblock, (size_t)t->node_cap * 8 * sizeof(ChildRec)));
     BH_TRY(cudaMalloc(&t->pslot, (size_t)t->node_cap * sizeof(unsigned)));
     BH_TRY(cudaMalloc(&t->level_count, (BH_MAX_LEVEL + 2) * sizeof(unsigned)));
-    BH_TRY(cudaMalloc(&t->flags, 4 * sizeof(unsigned)));
-    BH_TRY(cudaMemset(t->flags, 0, 4 * sizeof(unsigned)));
+    BH_TRY(cudaMalloc(&t->flags, 8 * sizeof(unsigned)));
+    BH_TRY(cudaMemset(t->flags, 0, 8 * sizeof(unsigned)));
     BH_TRY(cudaMalloc(&t->bbox, 2 * sizeof(double)));
     BH_TRY(cudaMalloc(&t->hist, ((size_t)256 * t->sort_blocks + 256) * sizeof(unsigned)));
     BH_TRY(cudaMalloc(&t->counters, 4 * sizeof(unsigned long long)));
@@ -757,7 +784,10 @@ static cudaError_t bh_after_sort(BhTree *t, const BhParams &p, cudaStream_t s, u
     ta.p = p;
     const unsigned max_own = sliced ? (p.own_end > p.own_begin ? min(p.own_end, n) - min(p.own_begin, n) : 0u) : n;
     if (max_own) {
-        const unsigned tgrid = (max_own + TRAV_WARPS * 32 - 1) / (TRAV_WARPS * 32);
+        unsigned tgrid = (max_own + TRAV_WARPS * 32 - 1) / (TRAV_WARPS * 32);
+#ifdef NB_BH_TRAV_DYNAMIC
+        tgrid = min(tgrid, 148u * (unsigned)NB_BH_TRAV_MINB); // resident: every warp loops over the counter
+#endif
 #ifdef NB_BH_ALWAYS_SELF
         const bool self = true;
 #else
@@ -765,9 +795,12 @@ static cudaError_t bh_after_sort(BhTree *t, const BhParams &p, cudaStream_t s, u
         // would use (the reference's is 0.01) is far above the bound
         const bool self = !(p.eps2 >= 1e-60);
 #endif
-        if (p.count_visits) traverse_kernel<true, true><<<tgrid, TRAV_WARPS * 32, 0, s>>>(ta);
-        else if (self) traverse_kernel<false, true><<<tgrid, TRAV_WARPS * 32, 0, s>>>(ta);
-        else traverse_kernel<false, false><<<tgrid, TRAV_WARPS * 32, 0, s>>>(ta);
+        static const int force_pf = getenv("NB_BH_PREFETCH") ? atoi(getenv("NB_BH_PREFETCH")) : -1;
+        const bool pf = force_pf >= 0 ? force_pf != 0 : false;
+        if (p.count_visits) traverse_kernel<true, true, false><<<tgrid, TRAV_WARPS * 32, 0, s>>>(ta);
+        else if (self) traverse_kernel<false, true, false><<<tgrid, TRAV_WARPS * 32, 0, s>>>(ta);
+        else if (pf) traverse_kernel<false, false, true><<<tgrid, TRAV_WARPS * 32, 0, s>>>(ta);
+        else traverse_kernel<false, false, false><<<tgrid, TRAV_WARPS * 32, 0, s>>>(ta);
         ++nl;
     }
     BH_TRY(stage_end(t, p, ST_TRAV, s));
