@@ -47,6 +47,9 @@ struct BhTree {
     double4 *spos = nullptr;               // x,y,z,m in Morton order
     unsigned *own = nullptr;               // sorted indices this rank integrates, Morton order
     unsigned *own_counts = nullptr;        // per-tile member counts / bases of the compaction
+    // the walk's schedule: records tested by each 128-body CTA in the last evaluation, and the
+    // order (heaviest first) in which the next one starts them
+    unsigned *cta_cost = nullptr, *cta_order = nullptr;
     // per internal node
     double4 *com = nullptr;   // centre of mass x,y,z + total mass
     int *child = nullptr;     // [node][8]: -1 empty, >= 0 body (sorted index), <= -2 node -(c+2)
