@@ -137,7 +137,10 @@ int nb_gather_slice(nb_engine *e, double *pos_rows, double *vel_rows);
 /* Advances n_steps of kick-drift-kick leapfrog: the time loop of propagation()
  * (serial/exhaustive.c:218-250, cuda/exhaustive.cu:135-151).  One fused
  * force+integrate launch per step; a run of n steps followed by nb_gather
- * with velocities costs n+1 force evaluations, like the reference. */
+ * with velocities costs n+1 force evaluations, like the reference.
+ * A Barnes-Hut engine with world > 1 lays its state out again every 32 steps (environment
+ * NB_BH_RELAYOUT_EVERY=K, the same on every rank; 0: never): bodies are dealt to the ranks along
+ * the Morton curve of the moment.  No value changes, only where a body lives. */
 int nb_step(nb_engine *e, int n_steps);
 
 /* Copies the current state out: what the reference reads back at

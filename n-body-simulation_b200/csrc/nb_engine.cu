@@ -160,6 +160,9 @@ struct nb_engine {
     // NB_DEBUG_OWN_SLICE="W:r" on a one-rank Barnes-Hut engine: lay the state out as W ranks would
     // and walk only rank r's bodies -- what one rank of a W-GPU run does, measured on one GPU
     unsigned dbg_world = 0, dbg_rank = 0, dbg_len = 0;
+    bool deal_ready = false;      // chunk_base is on the device (it depends on n, world and the piece count only)
+    int relayout_every = 0;       // Barnes-Hut, world > 1: steps between two re-layouts of the state (0: never)
+    int steps_since_layout = 0;
     // A Barnes-Hut evaluation is ~75 short launches with fixed arguments per (ping-pong side,
     // epilogue flags): captured once as a CUDA graph, replayed afterwards.
     struct BhGraph {
@@ -430,6 +433,10 @@ int deal_curve(nb_engine *e)
     const unsigned n = (unsigned)e->n;
     const unsigned world = e->dbg_world ? e->dbg_world : (unsigned)e->cfg.world;
     const unsigned len = e->dbg_world ? e->dbg_len : e->slice_units;
+    if (e->deal_ready) {
+        NB_CUDA(remap_chunks(e->morton_tmp, e->user_of, n, kDealChunk, e->chunk_base, e->stream));
+        return NB_OK;
+    }
     const unsigned full = n / kDealChunk, rag = n % kDealChunk;
     std::vector<unsigned> base(full + 1, 0u), fill(world, 0u), cap(world, 0u);
     for (unsigned r = 0; r < world; ++r) {
@@ -466,6 +473,7 @@ int deal_curve(nb_engine *e)
                             cudaMemcpyHostToDevice, e->stream));
     NB_CUDA(remap_chunks(e->morton_tmp, e->user_of, n, kDealChunk, e->chunk_base, e->stream));
     NB_CUDA(cudaStreamSynchronize(e->stream)); // `base` leaves scope
+    e->deal_ready = true;
     return NB_OK;
 }
 
@@ -476,6 +484,8 @@ void io_rows(const nb_engine *e, size_t *begin, size_t *count)
     *begin = b;
     *count = std::min(e->n - b, e->io_per);
 }
+
+int layout_from_stage(nb_engine *e, bool have_vel, bool fresh);
 
 // sliced: pos / vel hold only this rank's io rows; the other ranks' rows arrive over NVLink
 int upload(nb_engine *e, const double *pos, const double *vel, bool sliced)
@@ -504,6 +514,17 @@ int upload(nb_engine *e, const double *pos, const double *vel, bool sliced)
         if (!rc) rc = wait_gather(e);
         if (rc) return rc;
     }
+    return layout_from_stage(e, vel != nullptr, true);
+}
+
+// The staged rows (host packing, caller's order, on the device) become the device layout.
+// fresh: a new state from the host (classify the masses, clear the tree's overflow flags, reset
+// the step counter); otherwise the running state re-laid out (relayout below): nothing but the
+// order of the bodies on the device changes, and the host is not waited for.
+int layout_from_stage(nb_engine *e, bool have_vel, bool fresh)
+{
+    const size_t n = e->n;
+    const double *vel = have_vel ? e->stage_vel : nullptr;
     // equal masses (the usual N-body initial condition): the FP32 kernel drops m_j from its inner
     // loop and the epilogue multiplies by G*m.  Padding then has to be inert without a zero
     // mass: it is parked so far away that r^-3 underflows to exactly 0.  The masses are
@@ -511,11 +532,13 @@ int upload(nb_engine *e, const double *pos, const double *vel, bool sliced)
     const bool f64 = e->cfg.precision != NB_PREC_FP32;
     const bool classify = !e->bh && n > 0 && !(e->cfg.tune_flags & NB_TUNE_NO_UNIFORM) &&
                           (f64 || !(e->cfg.tune_flags & NB_TUNE_SCALAR_FP32));
-    NB_CUDA(mass_class(e->stage_pos, (unsigned)n, e->mass_cls, classify, f64, e->stream));
-    if (classify) e->st.kernel_launches++;
-    // overflow flags of the tree stay set between evaluations (a truncated tree must be caught
-    // at the next gather) but not across a new state
-    if (e->bh) NB_CUDA(cudaMemsetAsync(e->tree.flags, 0, 2 * sizeof(unsigned), e->stream));
+    if (fresh) {
+        NB_CUDA(mass_class(e->stage_pos, (unsigned)n, e->mass_cls, classify, f64, e->stream));
+        if (classify) e->st.kernel_launches++;
+        // overflow flags of the tree stay set between evaluations (a truncated tree must be caught
+        // at the next gather) but not across a new state
+        if (e->bh) NB_CUDA(cudaMemsetAsync(e->tree.flags, 0, 2 * sizeof(unsigned), e->stream));
+    }
     if (e->user_of) {
         // every rank sees all n bodies, so every rank derives the same order
         unsigned nl = 0;
@@ -539,6 +562,11 @@ int upload(nb_engine *e, const double *pos, const double *vel, bool sliced)
     NB_CUDA(pack_bodies(e->cfg.precision, e->stage_pos, vel ? e->stage_vel : nullptr, (unsigned)n,
                         e->n_units, e->q[0], e->q[1], e->vel, e->mass_cls, e->stream));
     e->st.kernel_launches++;
+    e->cur = 0;
+    e->vel_complete = true;
+    e->bh_pipe_pending = false; // all positions are local again: the next evaluation sorts them itself
+    e->steps_since_layout = 0;
+    if (!fresh) return NB_OK;
     unsigned cls[4] = {0u, 0u, 0u, 0u};
     NB_CUDA(cudaMemcpyAsync(cls, e->mass_cls, sizeof(cls), cudaMemcpyDeviceToHost, e->stream));
     NB_CUDA(cudaStreamSynchronize(e->stream)); // the caller's arrays are free again; cls is in
@@ -548,12 +576,29 @@ int upload(nb_engine *e, const double *pos, const double *vel, bool sliced)
     memcpy(&d0, &cls[2], sizeof(d0));
     e->uniform = cls[0] != 0u;
     e->uniform_m = f64 ? d0 : (double)m0;
-    e->cur = 0;
     e->state = SYNCED_NOACC;
-    e->vel_complete = true;
-    e->bh_pipe_pending = false; // all positions are local again: the next evaluation sorts them itself
     e->st.steps_done = 0;
     return NB_OK;
+}
+
+// Barnes-Hut on several ranks: a rank integrates the bodies it was dealt when the state was laid
+// out (pieces of the Morton curve of THAT moment).  As the bodies move, a rank's bodies spread over
+// the curve; 32 consecutive ones of its list are then no longer neighbours and their common walk
+// tests more records (16M bodies on 8 GPUs: +8 % after 80 steps of a Plummer sphere).  Every
+// relayout_every steps the state is therefore laid out again, on the device: velocities
+// all-gathered, state unpacked to the staged rows (caller's order) and packed from there exactly
+// as nb_upload does -- no value changes, only where it lives and who integrates it.  Collective;
+// called between two steps (state MIDSTEP: positions drifted, velocities half-kicked).
+int relayout(nb_engine *e)
+{
+    int rc = wait_gather(e);
+    if (rc) return rc;
+    if ((rc = ensure_vel_complete(e))) return rc;
+    const unsigned n = (unsigned)e->n;
+    NB_CUDA(unpack_bodies(e->cfg.precision, e->vel, n, 3, e->stage_vel, e->user_of, e->stream));
+    NB_CUDA(unpack_bodies(e->cfg.precision, e->q[e->cur], n, 4, e->stage_pos, e->user_of, e->stream));
+    e->st.kernel_launches += 2;
+    return layout_from_stage(e, true, false);
 }
 
 } // namespace
@@ -714,6 +759,10 @@ static int init_impl(nb_engine *e, const double *pos, const double *vel)
         return NB_E_INVALID;
     }
     e->bh_pipe = e->bh && c.world > 1 && e->n > 0 && !(c.tune_flags & NB_TUNE_REPLICATED_SORT);
+    if (e->bh && c.world > 1 && e->n > 1 && !(c.tune_flags & NB_TUNE_NO_REORDER)) {
+        const char *ev = getenv("NB_BH_RELAYOUT_EVERY"); // same value on every rank (the call is collective)
+        e->relayout_every = ev ? atoi(ev) : 32;
+    }
     e->bh_emulate_runs = (e->bh && c.world == 1) ? ((c.tune_flags >> 24) & 0xf) : 0;
     if (e->bh) {
         size_t n_keys = e->n;
@@ -859,6 +908,11 @@ int nb_step(nb_engine *e, int n_steps)
     struct Restore { nb_engine *e; ~Restore() { e->time_force = true; } } restore{e};
     for (int s = 0; s < n_steps; ++s) {
         e->time_force = (s == n_steps - 1);
+        if (e->relayout_every > 0 && e->state == MIDSTEP && e->steps_since_layout >= e->relayout_every) {
+            rc = relayout(e);
+            if (rc) return rc;
+        }
+        ++e->steps_since_layout;
         if (e->state == SYNCED_ACC) {
             NB_CUDA(kickdrift(e->cfg.precision, e->q[e->cur], e->q[e->cur ^ 1], e->vel, e->acc,
                               e->i_begin, e->i_end, (unsigned)e->n, e->cfg.dt, e->stream));

@@ -179,6 +179,38 @@ def test_barnes_hut_ranks_bitwise(nb, world):
         assert np.array_equal(acc, a1) and np.array_equal(p, p1) and np.array_equal(v, v1)
 
 
+@pytest.mark.parametrize("world,n,every", [(2, 10_000, 2), (2, 1000, 1), (2, 130, 3), (4, 10_000, 3),
+                                           (8, 10_000, 2)])
+def test_barnes_hut_relayout_keeps_every_bit(nb, monkeypatch, world, n, every):
+    """A multi-rank Barnes-Hut engine lays its state out again every K steps (bodies dealt to the
+    ranks along the Morton curve of the moment; 32 by default, forced to 1..3 here).  Nothing but
+    the place of a body on the devices may change: the state after 7 steps, stepped in one call and
+    in pieces, gathered whole and by slices, equals the one-rank state bit for bit."""
+    need(nb, world)
+    g = golden("10k_bodies_g1")
+    pm, vel = g["pos_xyzm"][:n].copy(), g["vel"][:n].copy()
+    kw = dict(precision=nb.PREC_FP64, algorithm=nb.ALGO_BARNES_HUT, dt=g["dt"])
+    with nb.Engine(pm, vel, **kw) as e:
+        e.step(7)
+        p1, v1 = e.gather()
+        ke1, pe1 = e.energy()
+    monkeypatch.setenv("NB_BH_RELAYOUT_EVERY", str(every))
+
+    def fn(e, r):
+        e.step(4)
+        e.step(1)
+        e.step(2)
+        b, c = e.io_slice()
+        ps, vs = e.gather_slice()
+        p, v = e.gather()
+        return p, v, ps, vs, b, c, e.energy()
+
+    for p, v, ps, vs, b, c, (ke, pe) in run_ranks(nb, world, fn, pm, vel, **kw):
+        assert np.array_equal(p, p1) and np.array_equal(v, v1)
+        assert np.array_equal(ps, p1[b:b + c]) and np.array_equal(vs, v1[b:b + c])
+        assert abs(ke - ke1) <= 1e-12 * abs(ke1) and abs(pe - pe1) <= 1e-12 * abs(pe1)
+
+
 @pytest.mark.parametrize("n", [2, 3, 129, 257, 1000])
 @pytest.mark.parametrize("flags", ["deal", "curve", "caller"])
 def test_barnes_hut_ragged_slices_and_orders(nb, n, flags):
