@@ -631,8 +631,8 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, NB_BH_TRAV_MINB) traverse_ker
 // previous evaluation (the bodies of CTA i are almost the same from one step to the next).  The
 // hardware hands out CTAs in index order; a walk through a dense core takes several times the
 // average ~0.8 ms, and when such CTAs come late the other SMs idle until they are done (ncu: SMs
-// idle 4 % of the kernel at 1M bodies, 8 % for one rank of eight at 16M).  Measured gain: 400k
-// Plummer 2.08 -> 1.98 ms, 1M 4.84 -> 4.82, one rank of eight at 16M 11.9 -> 11.65 ms.  A stable counting sort into 8 cost
+// idle 4 % of the kernel at 1M bodies, 8 % for one rank of eight at 16M).  Measured: 400k Plummer
+// 2.08 -> 1.98 ms; from 1M up nothing (see the launch site), so it runs for 151k..600k bodies.  A stable counting sort into 8 cost
 // classes (neighbours in a class stay neighbours: they share the tree's lines in L2), one CTA.
 // The order in which walks run does not touch any result.
 constexpr int ORDER_BINS = 8;
@@ -878,10 +878,13 @@ static cudaError_t bh_after_sort(BhTree *t, const BhParams &p, cudaStream_t s, u
     static const bool in_order = getenv("NB_BH_BODY_ORDER") != nullptr; // A/B: CTAs in body order
     const unsigned max_own_bodies =
         sliced ? (p.own_end > p.own_begin ? min(p.own_end, n) - min(p.own_begin, n) : 0u) : n;
-    // worth it between one resident grid (151k bodies) and ~4M bodies: beyond, the end of the
-    // kernel is < 1 % of it and the one-CTA sort costs more (16M: 81.7 -> 82.0 ms)
+    // worth it for a few resident grids' worth of bodies (one grid = 151k): 400k Plummer 2.08 ->
+    // 1.98 ms.  From 1M up the end of the kernel is a small part of it and the order costs as much
+    // as it gains (1M in the bench 4.85 -> 4.91 ms, uniform cube 3.07 -> 3.12, 16M 81.7 -> 82.0,
+    // the slowest of eight ranks at 16M unchanged); NB_BH_HEAVY_FIRST=1 forces it on
+    static const bool forced = getenv("NB_BH_HEAVY_FIRST") != nullptr;
     const bool lpt = !in_order && !p.count_visits && max_own_bodies > 148u * 8u * TRAV_WARPS * 32u &&
-                     max_own_bodies <= 4000000u;
+                     (forced || max_own_bodies <= 600000u);
     BH_TRY(stage_begin(t, p, ST_TRAV, s));
     if (lpt) { // more CTAs than fit at once: decide who starts first
         cta_order_kernel<<<1, 1024, 0, s>>>(t->cta_cost, t->cta_order, t->flags, n, sliced ? 1 : 0);
