@@ -684,7 +684,7 @@ namespace {
 struct VariantF32 {
     int nw, tq, minb, qpt;
 };
-constexpr int kNumVariants = 9;
+constexpr int kNumVariants = 13;
 constexpr VariantF32 kVariants[kNumVariants] = {
     {8, 64, 2, 0},  // 0 j-packed, 2 x 8 warps per SM, <=128 regs (round 1's large class)
     {4, 64, 4, 0},  // 1 medium: 4 x 4 warps per SM
@@ -695,6 +695,10 @@ constexpr VariantF32 kVariants[kNumVariants] = {
     {8, 64, 1, 2},  // 6 i-packed 8i, 1 x 8 warps, <=255 regs
     {8, 64, 1, 3},  // 7 i-packed 12i, 1 x 8 warps, <=255 regs
     {4, 64, 2, 2},  // 8 i-packed 8i, 2 x 4 warps, <=255 regs
+    {8, 128, 1, 2}, // 9 variant 6 with j-tiles of 128 quads (half the flushes into the FP64 sums)
+    {8, 32, 1, 2},  // 10 ... of 32 quads
+    {8, 256, 1, 2}, // 11 ... of 256 quads
+    {8, 192, 1, 2}, // 12 ... of 192 quads
 };
 #ifndef NB_F32_LARGE_VARIANT
 #define NB_F32_LARGE_VARIANT 6
@@ -774,6 +778,11 @@ cudaError_t plan_direct_f32(DirectPlan *plan, const SliceGeom &sg, int sm_count,
     const double work = (double)slice_bodies * (double)n_units * 4.0;
     const bool packed = !(tune_flags & 1);
     int v = work >= 3.5e8 ? (packed ? NB_F32_LARGE_VARIANT : 0) : 2;
+    // j-tiles of 128 quads instead of 64 halve the flushes of the FP32 partial sums into the FP64
+    // ones: 1M bodies 348.1 -> 343.5 ms; 256 quads: 341.7 ms, but too coarse a work unit below
+    // ~500k bodies (30k: 0.34 -> 0.44 ms) and, on several ranks, more padding (slices are whole tiles)
+    if (v == NB_F32_LARGE_VARIANT && v == 6)
+        v = (sg.own_units == sg.n_units && n_units >= 200000u) ? 11 : 9;
     const int forced = (tune_flags >> 8) & 0xf;
     if (forced >= 1 && forced <= kNumVariants) v = forced - 1;
     if (!packed && kVariants[v].qpt) v = 0; // the scalar A/B twin exists in the j-packed kernel only
@@ -798,6 +807,10 @@ cudaError_t plan_direct_f32(DirectPlan *plan, const SliceGeom &sg, int sm_count,
     case 5: err = prepare_ip<8, 64, 2, 2>(); occ = occupancy_ip<8, 64, 2, 2>(); break;
     case 6: err = prepare_ip<8, 64, 1, 2>(); occ = occupancy_ip<8, 64, 1, 2>(); break;
     case 7: err = prepare_ip<8, 64, 1, 3>(); occ = occupancy_ip<8, 64, 1, 3>(); break;
+    case 9: err = prepare_ip<8, 128, 1, 2>(); occ = occupancy_ip<8, 128, 1, 2>(); break;
+    case 10: err = prepare_ip<8, 32, 1, 2>(); occ = occupancy_ip<8, 32, 1, 2>(); break;
+    case 11: err = prepare_ip<8, 256, 1, 2>(); occ = occupancy_ip<8, 256, 1, 2>(); break;
+    case 12: err = prepare_ip<8, 192, 1, 2>(); occ = occupancy_ip<8, 192, 1, 2>(); break;
     default: err = prepare_ip<4, 64, 2, 2>(); occ = occupancy_ip<4, 64, 2, 2>(); break;
     }
     if (err != cudaSuccess) return err;
@@ -826,6 +839,10 @@ cudaError_t launch_direct_f32(const DirectPlan &plan, int geom, StepParams p, in
     case 5: return launch_ip<8, 64, 2, 2>(plan, p, mode, stream);
     case 6: return launch_ip<8, 64, 1, 2>(plan, p, mode, stream);
     case 7: return launch_ip<8, 64, 1, 3>(plan, p, mode, stream);
+    case 9: return launch_ip<8, 128, 1, 2>(plan, p, mode, stream);
+    case 10: return launch_ip<8, 32, 1, 2>(plan, p, mode, stream);
+    case 11: return launch_ip<8, 256, 1, 2>(plan, p, mode, stream);
+    case 12: return launch_ip<8, 192, 1, 2>(plan, p, mode, stream);
     default: return launch_ip<4, 64, 2, 2>(plan, p, mode, stream);
     }
 }

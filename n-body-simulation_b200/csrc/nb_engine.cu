@@ -720,7 +720,9 @@ static int init_impl(nb_engine *e, const double *pos, const double *vel)
     // force sum can be cut into "own slice" and "gathered" tiles
     const size_t units = (e->n + e->unit_bodies - 1) / e->unit_bodies;
     size_t per = (units + c.world - 1) / c.world;
-    const size_t align = f32 ? kSliceAlignF32 : kSliceAlignF64;
+    // FP32: the large size class cuts j into tiles of 128 quads (nb_direct_f32.cu); slices long
+    // enough to get it are whole tiles of that size, so the own-slice / gathered split stays possible
+    const size_t align = f32 ? (per >= 2048 ? 2 * kSliceAlignF32 : kSliceAlignF32) : kSliceAlignF64;
     if (c.world > 1) per = (per + align - 1) / align * align;
     if (per == 0) per = 1;
     if (per * (size_t)c.world * e->unit_bodies > 0x7fffffffu) {
