@@ -778,6 +778,9 @@ cudaError_t plan_direct_f32(DirectPlan *plan, const SliceGeom &sg, int sm_count,
     const double work = (double)slice_bodies * (double)n_units * 4.0;
     const bool packed = !(tune_flags & 1);
     int v = work >= 3.5e8 ? (packed ? NB_F32_LARGE_VARIANT : 0) : 2;
+    // in between (15k^2: 104 us against 113 for the small and 127 for the large class): the
+    // i-packed kernel with two CTAs of 4 warps per SM
+    if (packed && work >= 2.0e8 && work < 3.5e8) v = 8;
     // j-tiles of 128 quads instead of 64 halve the flushes of the FP32 partial sums into the FP64
     // ones: 1M bodies 348.1 -> 343.5 ms; 256 quads: 341.7 ms, but too coarse a work unit below
     // ~500k bodies (30k: 0.34 -> 0.44 ms) and, on several ranks, more padding (slices are whole tiles)

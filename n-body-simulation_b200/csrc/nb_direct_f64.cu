@@ -327,7 +327,9 @@ cudaError_t plan_direct_f64(DirectPlan *plan, const SliceGeom &sg, int sm_count,
     // (20k: 0.404 vs 0.412 ms medium; 30k: 0.859 vs 0.901; 100k: 9.24 vs 9.56 for round 1's
     // large class), small at 10k^2 and below
     const double work = (double)slice_units * (double)n_units;
-    int v = work >= 3.5e8 ? NB_F64_LARGE_VARIANT : (work >= 1.44e8 ? 1 : 2);
+    // (later scan, profiles/r2_mid_size_scan.txt: 10k^2 121.7 us large / 127.1 small / 129.3 medium;
+    // 15k^2 229.6 / 268.0 / 242.0 -- the large class from 10k^2)
+    int v = work >= 9.0e7 ? NB_F64_LARGE_VARIANT : 2;
     const int forced = (tune_flags >> 8) & 0xf;
     if (forced >= 1 && forced <= kNumVariants64) v = forced - 1;
     const VariantF64 &k = kVariants64[v];

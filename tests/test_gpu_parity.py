@@ -236,7 +236,7 @@ def test_all_size_classes(nb, variant, prec):
     assert rel_err(acc, g["acc0"]).max() <= (1e-12 if prec == "fp64" else 1e-5)
 
 
-@pytest.mark.parametrize("variant", [4, 5, 6, 7, 10, 12])
+@pytest.mark.parametrize("variant", [4, 5, 6, 7, 9, 10, 12])
 @pytest.mark.parametrize("masses", ["equal", "spread"])
 @pytest.mark.parametrize("n", [5, 1000, 10_000, 33_000])
 def test_fp32_ipacked_size_classes(nb, oracle_lib, variant, masses, n):
