@@ -201,6 +201,24 @@ typedef struct nb_tree_info {
 } nb_tree_info;
 int nb_tree_stats(nb_engine *e, nb_tree_info *out);
 
+/* No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, serving loops, harnesses that forbid it).
+ * The energy of nb_energy -- KE = 1/2 sum m v^2, unsoftened PE = -G sum_{i<j} m_i m_j / r_ij -- of n
+ * bodies the CALLER holds on `device`: d_pos_xyzm (4n doubles x,y,z,m) and d_vel_xyz (3n doubles)
+ * are device pointers in the host packing of nb_init; {KE, PE} is written to the device pointer
+ * d_ke_pe (2 doubles) by work enqueued on `stream` (a cudaStream_t; NULL = the default stream).
+ * The call does not synchronise and allocates nothing -- no cudaMalloc / cudaFree, no engine: the
+ * kernel's block partials live in a file-scope device array of the library, 32 KB on every GPU
+ * that loads it, which bounds n: n > NB_ENERGY_STATIC_MAX_BODIES is refused with NB_E_INVALID and
+ * a message in nb_last_error().  All calls on a device share that array (it keeps the last call's
+ * contents; each call overwrites what it reads, nothing needs clearing): calls that overlap on
+ * the GPU -- different streams, no dependency -- race; order them.  Same kernel and same
+ * summation order as nb_energy, so the two agree bit for bit on the same bodies in the same order.
+ * It selects `device` as the calling thread's current device. */
+#define NB_ENERGY_STATIC_MAX_BODIES 1048576
+int nb_energy_static(int device, const double *d_pos_xyzm, const double *d_vel_xyz, size_t n,
+                     double G, double *d_ke_pe, void *stream);
+
 int nb_sync(nb_engine *e);
 int nb_get_stats(nb_engine *e, nb_stats *out);
 

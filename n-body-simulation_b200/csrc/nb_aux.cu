@@ -5,6 +5,8 @@
 //   already stored (serial/exhaustive.c:221-232), and get_energy
 //   (common/get_energy.c:7-47) as an O(N^2) FP64 kernel.
 #include "nb_aux.cuh"
+#include <mutex>
+#include "../../include/nbody_engine.h"
 
 namespace nb {
 namespace {
@@ -333,6 +335,63 @@ cudaError_t energy_partials(const double *pos_xyzm, const double *vel_xyz, unsig
 {
     if (n == 0) return cudaSuccess;
     energy_kernel<<<energy_blocks(n), ETB, 0, s>>>(pos_xyzm, vel_xyz, n, partial);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------ energy without allocations ----
+// nb_energy_static (include/nbody_engine.h): energy_kernel above with its block partials in a
+// file-scope device array instead of the engine's cudaMalloc'ed buffer, for callers that may not
+// allocate (stream capture, serving loops).  Every GPU that loads the library holds the array
+// (32 KB + 256 B) until exit.  All calls on a device share it and it keeps the last call's
+// contents: a call overwrites the partials of every block it launches and reads only those, so
+// nothing has to be cleared -- but two calls that overlap on the GPU (different streams) race.
+constexpr unsigned kEnergyStaticMaxBlocks = NB_ENERGY_STATIC_MAX_BODIES / ETB / 2;
+static __device__ __align__(256) double g_energy_static_partial[2 * kEnergyStaticMaxBlocks];
+
+namespace {
+// partials added in block order, like nb_energy does on the host: the same bits
+__global__ void energy_static_finish_kernel(const double *__restrict__ partial, unsigned blocks,
+                                            double G, double *__restrict__ ke_pe)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    double ke = 0, pe = 0;
+    for (unsigned b = 0; b < blocks; ++b) {
+        ke += partial[2 * b];
+        pe += partial[2 * b + 1];
+    }
+    ke_pe[0] = 0.5 * ke;
+    ke_pe[1] = -G * pe;
+}
+
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+double *g_static_ptr[kMaxDevices]; // device address of g_energy_static_partial, per device
+} // namespace
+
+// In host code `g_energy_static_partial` is a stand-in for the symbol, not a device address:
+// the address a kernel may use comes from cudaGetSymbolAddress, once per device, with that
+// device current.
+cudaError_t energy_static(int device, const double *d_pos_xyzm, const double *d_vel_xyz, unsigned n,
+                          double G, double *d_ke_pe, cudaStream_t s)
+{
+    if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+    cudaError_t err = cudaSetDevice(device);
+    if (err != cudaSuccess) return err;
+    double *scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_static_mu);
+        if (!g_static_ptr[device]) {
+            void *p = nullptr;
+            err = cudaGetSymbolAddress(&p, g_energy_static_partial);
+            if (err != cudaSuccess) return err;
+            g_static_ptr[device] = static_cast<double *>(p);
+        }
+        scratch = g_static_ptr[device];
+    }
+    const unsigned blocks = energy_blocks(n);
+    if (blocks > kEnergyStaticMaxBlocks) return cudaErrorInvalidValue;
+    if (blocks) energy_kernel<<<blocks, ETB, 0, s>>>(d_pos_xyzm, d_vel_xyz, n, scratch);
+    energy_static_finish_kernel<<<1, 32, 0, s>>>(scratch, blocks, G, d_ke_pe);
     return cudaGetLastError();
 }
 

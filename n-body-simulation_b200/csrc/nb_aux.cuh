@@ -33,4 +33,10 @@ unsigned energy_blocks(unsigned n);
 cudaError_t energy_partials(const double *pos_xyzm, const double *vel_xyz, unsigned n,
                             double *partial, cudaStream_t s);
 
+// energy_kernel with its partials in a file-scope device array (no allocation); device pointers in
+// the host packing, result {KE, PE} written to d_ke_pe on stream s.  cudaErrorInvalidValue when n
+// exceeds NB_ENERGY_STATIC_MAX_BODIES.
+cudaError_t energy_static(int device, const double *d_pos_xyzm, const double *d_vel_xyz, unsigned n,
+                          double G, double *d_ke_pe, cudaStream_t s);
+
 } // namespace nb

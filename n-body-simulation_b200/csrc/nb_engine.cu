@@ -1119,6 +1119,22 @@ int nb_energy(nb_engine *e, double *KE, double *PE)
     return NB_OK;
 }
 
+int nb_energy_static(int device, const double *d_pos_xyzm, const double *d_vel_xyz, size_t n,
+                     double G, double *d_ke_pe, void *stream)
+{
+    if (!d_ke_pe || (n && (!d_pos_xyzm || !d_vel_xyz))) {
+        set_err("nb_energy_static", "null pointer");
+        return NB_E_INVALID;
+    }
+    if (n > (size_t)NB_ENERGY_STATIC_MAX_BODIES) {
+        set_err("nb_energy_static", "n exceeds NB_ENERGY_STATIC_MAX_BODIES (1048576): the static scratch array holds no more block partials");
+        return NB_E_INVALID;
+    }
+    NB_CUDA(energy_static(device, d_pos_xyzm, d_vel_xyz, (unsigned)n, G, d_ke_pe,
+                          static_cast<cudaStream_t>(stream)));
+    return NB_OK;
+}
+
 int nb_tree_stats(nb_engine *e, nb_tree_info *out)
 {
     if (!e || !out) return NB_E_INVALID;

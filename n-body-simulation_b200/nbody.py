@@ -31,7 +31,7 @@ SLICE_ALIGN = {PREC_FP32: 64, PREC_FP64: 128}  # units; nb_direct.cuh kSliceAlig
 ABI_SYMBOLS = ["nb_config_default", "nb_init", "nb_upload", "nb_step", "nb_gather",
                "nb_io_slice", "nb_upload_slice", "nb_gather_slice",
                "nb_frame_begin", "nb_frame_wait", "nb_host_alloc", "nb_host_free",
-               "nb_accelerations", "nb_energy", "nb_sync", "nb_get_stats", "nb_tree_stats", "nb_free",
+               "nb_accelerations", "nb_energy", "nb_energy_static", "nb_sync", "nb_get_stats", "nb_tree_stats", "nb_free",
                "nb_comm_id", "nb_strerror", "nb_last_error", "nb_device_count", "nb_version"]
 HOST_SYMBOLS = ["nbh_read_bodies", "nbh_parse_bodies", "nbh_free", "nbh_parse_times",
                 "nbh_write_frame", "nbh_format_frame", "nbh_format_lf", "nbh_write_bodies"]
@@ -98,6 +98,8 @@ def load_library():
     lib.nb_host_free.argtypes = [C.c_void_p]
     lib.nb_accelerations.argtypes = [C.c_void_p, C.c_void_p]
     lib.nb_energy.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    lib.nb_energy_static.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_double,
+                                     C.c_void_p, C.c_void_p]
     lib.nb_sync.argtypes = [C.c_void_p]
     lib.nb_get_stats.argtypes = [C.c_void_p, C.POINTER(NbStats)]
     lib.nb_tree_stats.argtypes = [C.c_void_p, C.POINTER(NbTreeInfo)]
@@ -139,6 +141,17 @@ def load_host_library():
 def _check(lib, rc, what):
     if rc != 0:
         raise NbodyError(rc, what, (lib.nb_strerror(rc).decode(), lib.nb_last_error().decode()))
+
+
+ENERGY_STATIC_MAX_BODIES = 1048576
+
+
+def energy_static(d_pos_ptr, d_vel_ptr, n, d_ke_pe_ptr, G=1.0, device=0, stream=None):
+    """nb_energy_static: DEVICE pointers (ints) in the host packing, result written to the device
+    pointer d_ke_pe_ptr on `stream`; allocates nothing and does not synchronise."""
+    lib = load_library()
+    _check(lib, lib.nb_energy_static(int(device), d_pos_ptr, d_vel_ptr, int(n), float(G),
+                                     d_ke_pe_ptr, stream), "nb_energy_static")
 
 
 def device_count():
