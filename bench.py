@@ -913,10 +913,9 @@ def run_gpu_arm(args):
     if rank == 0:
         roof = direct_roofline(nb, prec, uni, my_rows, st0.n_padded, force_ms / args.steps, clocks)
         # one ncu --set full capture of this very launch (1M bodies, FP32, one GPU):
-        # dram__bytes_read.sum + dram__bytes_write.sum (profiles/r2_direct_f32_ip_ncu_full.csv:
-        # 28.84 MB + 1.90 MB, captured with 64-quad j-tiles; the shipped 256-quad tiles read the
-        # same arrays); other shapes were not captured
-        roof["traffic"] = 30742016 if (n == 1_000_000 and world == 1 and prec == nb.PREC_FP32 and uni) else None
+        # dram__bytes_read.sum + dram__bytes_write.sum (profiles/r2_direct_f32_ip_ncu_full.csv,
+        # the shipped 256-quad-tile kernel: 28.94 MB + 1.52 MB); other shapes were not captured
+        roof["traffic"] = 30467072 if (n == 1_000_000 and world == 1 and prec == nb.PREC_FP32 and uni) else None
         roof["traffic_note"] = ("bytes per launch from ncu (dram read + write); the algorithmic 64 B/body "
                                 "include the 32 MB of writes, which leave L2 only after the launch. "
                                 "The kernel is FMA-bound: HBM traffic is ~1e-4 of the time budget")
