@@ -1,7 +1,10 @@
 #!/usr/bin/env python3
 """Short view of a bench.py JSON line (the last JSON line of the file)."""
 import json
+import signal
 import sys
+
+signal.signal(signal.SIGPIPE, signal.SIG_DFL)
 
 for path in sys.argv[1:]:
     line = [l for l in open(path).read().splitlines() if l.startswith("{")][-1]
